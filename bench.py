@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py -- images/sec of the InferenceBolt hot path (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--preset cifar-lenet5]
+
+A "step" is one pass of the hot path over one batch of synthetic images.  Reported on ONE JSON line:
+  value      T0: device-resident fp32 NHWC -> probabilities, whole job (all ranks), CUDA events, max over ranks
+  e2e        T1: the same metric through the C ABI with HOST buffers (sib_submit_f32 / sib_poll): pinned staging,
+             H2D, kernels, D2H inside the timed region
+  roofline   dominant kernel vs MEASURED_PEAKS.json (HBM): algorithmic bytes = (H*W*C*4 + n_classes*4) per image
+  cpu_baseline  the CPU oracle (a port of the reference's per-tuple execute(), batch 1 per call) on the host cores
+Under torchrun (N>1) every rank drives its own GPU with its own engine (executor -> GPU = task index mod N,
+MainTopology.java:62); no collective touches the data path, torch.distributed is the barrier and the max.
+
+--impl reference times the reference's CPU implementation of the path (the oracle port: the reference itself is
+Java + TF-Java and cannot run here) on all host cores, rank 0 only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "images/sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--preset", default="cifar-lenet5")
+    ap.add_argument("--batch", type=int, default=16384, help="images per step per GPU")
+    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "fp16", "bf16"])
+    ap.add_argument("--no-guard", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------- clocks
+
+class ClockSampler:
+    """nvidia-smi sampling during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.lines: list[str] = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------- CPU arm
+
+def cpu_per_tuple(model, seconds: float, threads: int = 0):
+    """The reference's shape on the host cores: one forward per image (batch 1 per call, InferenceBolt.java:81-85),
+    `threads` executors each owning a contiguous share. Bounded by wall time. -> (img/s, cores, sample text)."""
+    import oracle
+    import sib_b200 as sib
+    om = oracle.Model(model.to_blob())
+    cores = oracle.max_threads() if threads <= 0 else threads
+    chunk = 256 * cores
+    x = sib.modelspec.synthetic_images(model, 0, chunk)
+    om.forward(x[:cores], threads=cores)  # warm
+    done, t0 = 0, time.perf_counter()
+    while True:
+        om.forward(x, threads=cores)
+        done += chunk
+        dt = time.perf_counter() - t0
+        if dt >= seconds:
+            break
+    return done / dt, cores, f"{done} images of {model.name} (D2 seed 1234), batch 1 per call, {dt:.1f} s wall"
+
+
+def run_reference(args):
+    """--impl reference: the CPU port of execute()'s model call on all host cores; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import sib_b200 as sib
+    model = sib.modelspec.make_preset(args.preset)
+    per_step = max(1.0, min(8.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_per_tuple(model, 0.2)
+    vals = []
+    t0 = time.perf_counter()
+    sample = ""
+    for _ in range(args.steps):
+        v, cores, sample = cpu_per_tuple(model, per_step)
+        vals.append(v)
+    wall = time.perf_counter() - t0
+    value = statistics.mean(vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, model, "fp32-cpu"),
+        "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
+                         "sample": f"per step: {sample}; oracle/sib_oracle.c (TF-Java/Jackson cannot run: no JVM)"},
+        "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, model, precision: str) -> dict:
+    return {"workload": f"{model.name} ({model.h}x{model.w}x{model.c} -> softmax {model.n_classes}), "
+                        f"{args.batch} images per step per GPU, SURVEY.md D2 synthetic pixels and weights",
+            "preset": model.name, "images_per_step_per_gpu": args.batch, "precision": precision,
+            "parallelism": f"executor-per-gpu x{args.gpus}, shuffle grouping, no collective",
+            "l2": "4 rotating input buffers per GPU, each step's batch is read from HBM (4 x batch x image bytes > 126 MB L2)"}
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import sib_b200 as sib
+    from importlib import import_module
+    sharding = import_module("sib_b200.sharding")
+    native = sib.native
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ngpu = torch.cuda.device_count()
+    dev = sharding.device_for_task(local, ngpu)
+    torch.cuda.set_device(dev)
+
+    model = sib.modelspec.make_preset(args.preset)
+    blob = model.to_blob()
+    prec_name = args.precision
+    if prec_name == "auto":
+        prec_name = sib.default_bench_precision()
+    prec = {"fp32": native.PREC_FP32, "bf16": native.PREC_BF16, "fp16": getattr(native, "PREC_FP16", 1)}[prec_name]
+    B = args.batch
+    eng = native.Engine(blob, device=dev, task_index=rank, max_batch=B, deadline_us=200, precision=prec,
+                        n_slots=4, guard=not args.no_guard)
+    nc, img = model.n_classes, model.img_elems
+
+    # ---- T0: device-resident. 4 rotating batches so every step streams its input from HBM, not L2.
+    R = 4
+    host_batches = [sib.modelspec.synthetic_images(model, 100 + rank * R + r, B) for r in range(R)]
+    d_in = [torch.from_numpy(h).cuda() for h in host_batches]
+    d_probs = torch.empty((B, nc), dtype=torch.float32, device="cuda")
+    d_argmax = torch.empty((B,), dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream()
+
+    def step(i):
+        eng.forward_device(d_in[i % R].data_ptr(), B, d_probs.data_ptr(), 0, d_argmax.data_ptr(), stream.cuda_stream)
+
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    launches0 = eng.stats().kernel_launches
+    sampler = ClockSampler(dev)
+    if rank == 0:
+        sampler.start()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    torch.cuda.synchronize()
+    evs[0].record(stream)
+    for i in range(args.steps):
+        step(i)
+        evs[i + 1].record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = eng.stats().kernel_launches - launches0
+    t0_local = evs[0].elapsed_time(evs[-1]) * 1e-3
+    step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
+    units, secs = sharding.aggregate(B * args.steps, t0_local, dist if world > 1 else None)
+    value = units / secs
+    checksum = float(d_probs.sum().item())  # every row sums to 1: B
+    assert abs(checksum - B) < 1e-2 * B, checksum
+
+    # ---- T1: host buffers through the C ABI (submit chunks of 1024 images; engine batches to B)
+    e2e = None
+    if not args.skip_e2e:
+        chunk = min(1024, B)
+        per_step = B // chunk
+        def e2e_steps(n_steps, first):
+            got = 0
+            for s in range(n_steps):
+                h = host_batches[(first + s) % R]
+                for c in range(per_step):
+                    part = h[c * chunk:(c + 1) * chunk]
+                    while True:
+                        rc = eng.submit_f32(s * per_step + c, part)
+                        if rc == native.EAGAIN:
+                            got += _poll_count(eng, 200)
+                            continue
+                        if rc < 0:
+                            raise native.SibError(rc, "sib_submit_f32")
+                        break
+                got += _poll_count(eng, 0)
+            eng.flush()
+            while got < n_steps * B:
+                got += _poll_count(eng, -1)
+            return got
+        e2e_steps(max(1, min(args.warmup, 3)), 0)
+        st0 = eng.stats()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t_a = time.perf_counter()
+        n_e2e = max(2, min(args.steps, 10))
+        e2e_steps(n_e2e, 1)
+        torch.cuda.synchronize()
+        t_b = time.perf_counter()
+        if world > 1:
+            dist.barrier()
+        st1 = eng.stats()
+        u2, s2 = sharding.aggregate(B * n_e2e, t_b - t_a, dist if world > 1 else None)
+        e2e = {"value": u2 / s2, "unit": "images/s", "level": "T1: sib_submit_f32/sib_poll, host fp32 buffers",
+               "h2d_bytes_per_step": (st1.h2d_bytes - st0.h2d_bytes) // n_e2e,
+               "d2h_bytes_per_step": (st1.d2h_bytes - st0.d2h_bytes) // n_e2e, "steps": n_e2e}
+
+    guard_n = eng.stats().guard_recomputed
+    eng.close()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = json.load(open(pk))
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    bpi = model.bytes_per_image()
+    k_ms = statistics.median(step_ms)  # one step = one launch of the forward kernel (+ guard launch)
+    achieved = B * bpi / (k_ms * 1e-3) * 1e-9
+    traffic = None
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            traffic = json.load(open(tr)).get(f"{model.name}:{prec_name}:{B}")
+        except Exception:
+            traffic = None
+    line = {
+        "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": {"fp32": "f32", "fp16": "f16 operands, f32 accumulate",
+                                       "bf16": "bf16 operands, f32 accumulate"}[prec_name],
+        "data": "synthetic", "config": workload_config(args, model, prec_name),
+        "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+                     "kernel_ms": k_ms, "algorithmic_bytes_per_image": bpi, "images_per_launch": B,
+                     "flops_per_image": model.flops_per_image()},
+        "clocks": clocks, "guard_recomputed_images": int(guard_n),
+    }
+    if not args.skip_cpu:
+        v, cores, sample = cpu_per_tuple(model, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _poll_count(eng, timeout_us):
+    n, res = eng.poll_raw(4096, timeout_us)
+    return sum(res[i].n for i in range(n))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,538 @@
+// sib_engine.cpp -- the per-executor engine behind the C ABI: device selection, weight upload, and the pinned-host
+// micro-batcher keyed on batch size and deadline.
+//
+// What it replaces in the reference (file:line relative to src/main/java/dke/model/):
+//   prepare(): SavedModelBundle.load + session()                     InferenceBolt.java:43-62  -> Engine::open
+//   execute(): one Session.run per tuple, strictly serial, batch = 1  InferenceBolt.java:69-100 -> submit_* / poll
+// Tuples from one executor are packed into fp32 NHWC batches in pinned host slots; a slot is launched when it holds
+// max_batch images (flush-by-size) or when its oldest tuple is deadline_us old (flush-by-deadline, helper thread).
+// Each launch is H2D copy -> forward kernel(s) -> D2H copy on the slot's own stream, so consecutive slots overlap
+// copy and compute. Results come back in submission order, one per input tuple (emit+ack order, :98-99).
+// There is no CPU fallback: without a CUDA device open() fails with SIB_ECUDA.
+#include <cuda_runtime_api.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <thread>
+
+#include "sib_internal.hpp"
+
+namespace sib {
+
+using Clock = std::chrono::steady_clock;
+
+#define CU_TRY(expr)                                                                                  \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess) {                                                                      \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                            \
+            return SIB_ECUDA;                                                                         \
+        }                                                                                             \
+    } while (0)
+
+struct Entry {
+    uint64_t tag;
+    int n, offset;
+};
+
+struct DevBufs {  // one forward's worth of device memory
+    float* d_in = nullptr;
+    float* d_probs = nullptr;
+    float* d_logits = nullptr;
+    int32_t* d_argmax = nullptr;
+    GuardScratch guard;
+};
+
+struct Slot {
+    enum State { FREE, FILLING, INFLIGHT, READY, HANDED };
+    State state = FREE;
+    float* h_in = nullptr;       // pinned, max_batch x img
+    float* h_probs = nullptr;    // pinned, max_batch x ncls
+    int32_t* h_argmax = nullptr; // pinned
+    int32_t* h_guard_n = nullptr; // pinned, 1
+    DevBufs dev;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    std::vector<Entry> entries;
+    size_t next_entry = 0;
+    int images = 0;
+    int status = SIB_OK;
+    Clock::time_point first_ts;
+};
+
+}  // namespace sib
+
+using namespace sib;
+
+struct sib_engine {
+    ModelDesc model;
+    DeviceModel dm{};
+    sib_config cfg{};
+    int device = 0;
+    float* d_weights = nullptr;
+    Bf16Weights bf16{};
+    std::vector<Slot> slots;
+    int filling = -1;
+    std::deque<int> fifo;  // launched slots, submission order
+    std::mutex mu;
+    std::condition_variable cv;
+    std::thread deadline_thread;
+    bool closing = false;
+    sib_stats stats{};
+    // synchronous path
+    std::mutex sync_mu;
+    Slot sync_slot;
+    DevBufs dev_scratch;  // guard scratch for sib_forward_device
+
+    int alloc_dev(DevBufs& d, bool with_io);
+    void free_dev(DevBufs& d);
+    int alloc_slot(Slot& s);
+    void free_slot(Slot& s);
+    int run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax, GuardScratch* g,
+                    cudaStream_t st);
+    int launch_locked(int si, int reason);
+    void deadline_main();
+};
+
+int sib_engine::alloc_dev(DevBufs& d, bool with_io) {
+    const size_t mb = (size_t)cfg.max_batch, nc = model.n_classes;
+    if (with_io) {
+        CU_TRY(cudaMalloc((void**)&d.d_in, mb * model.img_elems * sizeof(float)));
+        CU_TRY(cudaMalloc((void**)&d.d_probs, mb * nc * sizeof(float)));
+        CU_TRY(cudaMalloc((void**)&d.d_logits, mb * nc * sizeof(float)));
+        CU_TRY(cudaMalloc((void**)&d.d_argmax, mb * sizeof(int32_t)));
+    }
+    if (cfg.precision == SIB_PREC_BF16) {
+        CU_TRY(cudaMalloc((void**)&d.guard.d_margin, mb * sizeof(float)));
+        CU_TRY(cudaMalloc((void**)&d.guard.d_list, mb * sizeof(int32_t)));
+        CU_TRY(cudaMalloc((void**)&d.guard.d_count, 2 * sizeof(int32_t)));
+        CU_TRY(cudaMemset(d.guard.d_count, 0, 2 * sizeof(int32_t)));
+    }
+    return SIB_OK;
+}
+
+void sib_engine::free_dev(DevBufs& d) {
+    cudaFree(d.d_in); cudaFree(d.d_probs); cudaFree(d.d_logits); cudaFree(d.d_argmax);
+    cudaFree(d.guard.d_margin); cudaFree(d.guard.d_list); cudaFree(d.guard.d_count);
+    d = DevBufs{};
+}
+
+int sib_engine::alloc_slot(Slot& s) {
+    const size_t mb = (size_t)cfg.max_batch, nc = model.n_classes;
+    CU_TRY(cudaHostAlloc((void**)&s.h_in, mb * model.img_elems * sizeof(float), cudaHostAllocDefault));
+    CU_TRY(cudaHostAlloc((void**)&s.h_probs, mb * nc * sizeof(float), cudaHostAllocDefault));
+    CU_TRY(cudaHostAlloc((void**)&s.h_argmax, mb * sizeof(int32_t), cudaHostAllocDefault));
+    CU_TRY(cudaHostAlloc((void**)&s.h_guard_n, 2 * sizeof(int32_t), cudaHostAllocDefault));
+    s.h_guard_n[0] = 0;
+    int r = alloc_dev(s.dev, true);
+    if (r) return r;
+    CU_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+    s.entries.reserve(256);
+    return SIB_OK;
+}
+
+void sib_engine::free_slot(Slot& s) {
+    if (s.stream) cudaStreamSynchronize(s.stream);
+    cudaFreeHost(s.h_in); cudaFreeHost(s.h_probs); cudaFreeHost(s.h_argmax); cudaFreeHost(s.h_guard_n);
+    free_dev(s.dev);
+    if (s.done) cudaEventDestroy(s.done);
+    if (s.stream) cudaStreamDestroy(s.stream);
+    s = Slot{};
+}
+
+// One forward pass on device-resident data. BF16: tensor-core kernel, then the fp32 guard over low-margin images.
+int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
+                            GuardScratch* g, cudaStream_t st) {
+    int e;
+    if (cfg.precision == SIB_PREC_FP32) {
+        e = launch_forward_fp32(dm, d_in, n, nullptr, nullptr, d_probs, d_logits, d_argmax, nullptr, st);
+        stats.kernel_launches += 1;
+    } else {
+        const bool guard = cfg.guard != 0;
+        e = launch_forward_bf16(bf16, dm, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, st);
+        stats.kernel_launches += 1;
+        if (!e && guard) {
+            e = launch_forward_fp32(dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, nullptr, st);
+            stats.kernel_launches += 1;
+        }
+    }
+    if (e) {
+        set_error(std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)e));
+        return SIB_ECUDA;
+    }
+    return SIB_OK;
+}
+
+int sib_engine::launch_locked(int si, int reason) {
+    Slot& s = slots[si];
+    cudaSetDevice(device);
+    const size_t nc = model.n_classes;
+    int rc = SIB_OK;
+    auto chk = [&](cudaError_t e, const char* what) {
+        if (e != cudaSuccess && rc == SIB_OK) {
+            set_error(std::string(what) + ": " + cudaGetErrorString(e));
+            rc = SIB_ECUDA;
+        }
+    };
+    const size_t in_bytes = (size_t)s.images * model.img_elems * sizeof(float);
+    chk(cudaMemcpyAsync(s.dev.d_in, s.h_in, in_bytes, cudaMemcpyHostToDevice, s.stream), "H2D");
+    if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
+    chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)s.images * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream), "D2H probs");
+    chk(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)s.images * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H argmax");
+    size_t d2h = (size_t)s.images * (nc * sizeof(float) + sizeof(int32_t));
+    if (cfg.precision == SIB_PREC_BF16 && cfg.guard) {
+        chk(cudaMemcpyAsync(s.h_guard_n, s.dev.guard.d_count, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H guard count");
+        d2h += sizeof(int32_t);
+    }
+    chk(cudaEventRecord(s.done, s.stream), "event record");
+    s.status = rc;
+    s.state = Slot::INFLIGHT;
+    s.next_entry = 0;
+    fifo.push_back(si);
+    if (filling == si) filling = -1;
+    stats.batches++;
+    stats.h2d_bytes += in_bytes;
+    stats.d2h_bytes += d2h;
+    if (reason == 0) stats.flush_by_size++;
+    else if (reason == 1) stats.flush_by_deadline++;
+    else stats.flush_explicit++;
+    int b = 0;
+    while (b < 15 && (1 << (b + 1)) <= s.images) b++;
+    stats.batch_hist[b]++;
+    cv.notify_all();
+    return rc;
+}
+
+void sib_engine::deadline_main() {
+    cudaSetDevice(device);
+    std::unique_lock<std::mutex> lk(mu);
+    while (!closing) {
+        if (filling < 0 || slots[filling].images == 0) {
+            cv.wait(lk);
+            continue;
+        }
+        const int si = filling;
+        const auto due = slots[si].first_ts + std::chrono::microseconds(cfg.deadline_us);
+        if (Clock::now() >= due) {
+            launch_locked(si, 1);
+            continue;
+        }
+        cv.wait_until(lk, due);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+
+extern "C" int sib_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+extern "C" int sib_model_describe(const void* blob, size_t n, sib_model_info* out) {
+    ModelDesc m;
+    std::string err;
+    int r = parse_model(blob, n, &m, &err);
+    if (r) { set_error(err); return r; }
+    if (out) {
+        out->in_h = m.in_h; out->in_w = m.in_w; out->in_c = m.in_c; out->n_layers = m.n_layers;
+        out->n_classes = m.n_classes; out->n_weights = m.n_weights;
+        out->flops_per_image = m.flops_per_image;
+        out->bytes_per_image = (int64_t)m.img_elems * 4 + (int64_t)m.n_classes * 4;
+    }
+    return SIB_OK;
+}
+
+extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucfg, sib_engine** out) {
+    if (!out) return SIB_EINVAL;
+    *out = nullptr;
+    sib_engine* e = new sib_engine();
+    std::string err;
+    int r = parse_model(blob, n, &e->model, &err);
+    if (r) { set_error(err); delete e; return r; }
+    sib_config c{};
+    if (ucfg) c = *ucfg;
+    else { c.device = -1; c.guard = 1; }
+    if (c.max_batch <= 0) c.max_batch = 4096;
+    if (c.deadline_us <= 0) c.deadline_us = 200;
+    if (c.n_slots < 2) c.n_slots = 4;
+    if (c.guard_tau <= 0.0f) c.guard_tau = 0.05f;
+    if (c.precision != SIB_PREC_BF16 && c.precision != SIB_PREC_FP32) {
+        set_error("precision must be SIB_PREC_BF16 or SIB_PREC_FP32");
+        delete e;
+        return SIB_EINVAL;
+    }
+    int ndev = sib_device_count();
+    if (ndev <= 0) {
+        set_error("no CUDA device visible: libsib has no CPU fallback");
+        delete e;
+        return SIB_ECUDA;
+    }
+    if (c.device < 0) c.device = (c.task_index < 0 ? 0 : c.task_index) % ndev;  // executor -> GPU, MainTopology.java:62
+    if (c.device >= ndev) { set_error("device ordinal out of range"); delete e; return SIB_EINVAL; }
+    if (c.precision == SIB_PREC_BF16 && !bf16_supported(e->model)) {
+        set_error("SIB_PREC_BF16 covers the LeNet-5 presets (mnist-lenet5, cifar-lenet5); open this model with SIB_PREC_FP32");
+        delete e;
+        return SIB_EINVAL;
+    }
+    e->cfg = c;
+    e->device = c.device;
+    auto fail = [&](int code) { sib_engine_close(e); return code; };
+    if (cudaSetDevice(e->device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(SIB_ECUDA); }
+    const ModelDesc& m = e->model;
+    if (cudaMalloc((void**)&e->d_weights, m.weights.size() * sizeof(float)) != cudaSuccess ||
+        cudaMemcpy(e->d_weights, m.weights.data(), m.weights.size() * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("weight upload failed");
+        return fail(SIB_ECUDA);
+    }
+    DeviceModel& dm = e->dm;
+    dm.in_h = m.in_h; dm.in_w = m.in_w; dm.in_c = m.in_c; dm.n_layers = m.n_layers; dm.n_classes = m.n_classes;
+    dm.img_elems = m.img_elems; dm.max_store_act = m.max_store_act;
+    std::memcpy(dm.layer, m.layer, sizeof(LayerDesc) * kMaxLayers);
+    dm.weights = e->d_weights;
+    if (fp32_smem_bytes(dm) > 227 * 1024) { set_error("model activations exceed shared memory"); return fail(SIB_EINVAL); }
+    if (c.precision == SIB_PREC_BF16) {
+        r = bf16_prepare(m, &e->bf16);
+        if (r) return fail(r);
+    }
+    e->slots.resize(c.n_slots);
+    for (auto& s : e->slots)
+        if ((r = e->alloc_slot(s)) != SIB_OK) return fail(r);
+    if ((r = e->alloc_slot(e->sync_slot)) != SIB_OK) return fail(r);
+    if ((r = e->alloc_dev(e->dev_scratch, false)) != SIB_OK) return fail(r);
+    e->deadline_thread = std::thread([e] { e->deadline_main(); });
+    *out = e;
+    return SIB_OK;
+}
+
+extern "C" int sib_engine_close(sib_engine* e) {
+    if (!e) return SIB_EINVAL;
+    {
+        std::unique_lock<std::mutex> lk(e->mu);
+        if (e->filling >= 0 && e->slots[e->filling].images > 0) e->launch_locked(e->filling, 2);
+        e->closing = true;
+        e->cv.notify_all();
+    }
+    if (e->deadline_thread.joinable()) e->deadline_thread.join();
+    cudaSetDevice(e->device);
+    for (auto& s : e->slots) e->free_slot(s);
+    e->free_slot(e->sync_slot);
+    e->free_dev(e->dev_scratch);
+    bf16_release(&e->bf16);
+    cudaFree(e->d_weights);
+    delete e;
+    return SIB_OK;
+}
+
+extern "C" int sib_engine_info(sib_engine* e, sib_model_info* out, sib_config* eff) {
+    if (!e) return SIB_EINVAL;
+    if (out) {
+        const ModelDesc& m = e->model;
+        out->in_h = m.in_h; out->in_w = m.in_w; out->in_c = m.in_c; out->n_layers = m.n_layers;
+        out->n_classes = m.n_classes; out->n_weights = m.n_weights;
+        out->flops_per_image = m.flops_per_image;
+        out->bytes_per_image = (int64_t)m.img_elems * 4 + (int64_t)m.n_classes * 4;
+    }
+    if (eff) *eff = e->cfg;
+    return SIB_OK;
+}
+
+// Finds (or starts) the slot to append n images to. Returns slot index or a negative code. Caller holds mu.
+static int slot_for(sib_engine* e, int n) {
+    if (n > e->cfg.max_batch) { set_error("tuple holds more images than max_batch"); return SIB_ECAP; }
+    if (e->filling >= 0 && e->slots[e->filling].images + n > e->cfg.max_batch) e->launch_locked(e->filling, 0);
+    if (e->filling < 0) {
+        for (size_t i = 0; i < e->slots.size(); i++) {
+            if (e->slots[i].state == Slot::FREE) {
+                Slot& s = e->slots[i];
+                s.state = Slot::FILLING;
+                s.images = 0;
+                s.entries.clear();
+                s.next_entry = 0;
+                s.status = SIB_OK;
+                e->filling = (int)i;
+                break;
+            }
+        }
+        if (e->filling < 0) { set_error("all batch slots busy: poll first"); return SIB_EAGAIN; }
+    }
+    return e->filling;
+}
+
+static void appended(sib_engine* e, int si, uint64_t tag, int n) {
+    Slot& s = e->slots[si];
+    if (s.images == 0) {
+        s.first_ts = Clock::now();
+        e->cv.notify_all();  // arm the deadline thread
+    }
+    s.entries.push_back(Entry{tag, n, s.images});
+    s.images += n;
+    e->stats.tuples++;
+    e->stats.images += (uint64_t)n;
+    if (s.images >= e->cfg.max_batch) e->launch_locked(si, 0);
+}
+
+extern "C" int sib_submit_f32(sib_engine* e, uint64_t tag, const float* nhwc, int n) {
+    if (!e || !nhwc || n <= 0) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (e->closing) return SIB_ECLOSED;
+    int si = slot_for(e, n);
+    if (si < 0) return si;
+    Slot& s = e->slots[si];
+    std::memcpy(s.h_in + (size_t)s.images * e->model.img_elems, nhwc, (size_t)n * e->model.img_elems * sizeof(float));
+    appended(e, si, tag, n);
+    return n;
+}
+
+extern "C" int sib_submit_json(sib_engine* e, uint64_t tag, const char* utf8, size_t len) {
+    if (!e || !utf8) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (e->closing) return SIB_ECLOSED;
+    const ModelDesc& m = e->model;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        int si = slot_for(e, 1);
+        if (si < 0) return si;
+        Slot& s = e->slots[si];
+        const long room = (long)(e->cfg.max_batch - s.images) * (long)m.img_elems;
+        int64_t dims[4];
+        long nf = json_decode(utf8, len, s.h_in + (size_t)s.images * m.img_elems, room, dims);
+        if (nf == SIB_EJSON) { set_error("malformed instances JSON"); return SIB_EJSON; }
+        if (nf == SIB_ESHAPE) { set_error("instances is not a rectangular rank-4 array"); return SIB_ESHAPE; }
+        if (nf != SIB_ECAP && nf < 0) return (int)nf;
+        if (dims[1] != m.in_h || dims[2] != m.in_w || dims[3] != m.in_c) {
+            set_error("instances HxWxC does not match the model input");
+            return SIB_ESHAPE;
+        }
+        if (dims[0] > e->cfg.max_batch) { set_error("tuple holds more images than max_batch"); return SIB_ECAP; }
+        if (nf == SIB_ECAP) {
+            // did not fit behind the tuples already queued: launch those and decode again into a fresh slot
+            if (s.images == 0) return SIB_ECAP;
+            e->launch_locked(si, 0);
+            continue;
+        }
+        appended(e, si, tag, (int)dims[0]);
+        return (int)dims[0];
+    }
+    return SIB_EAGAIN;
+}
+
+extern "C" int sib_flush(sib_engine* e) {
+    if (!e) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (e->filling >= 0 && e->slots[e->filling].images > 0) return e->launch_locked(e->filling, 2);
+    return SIB_OK;
+}
+
+extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us) {
+    if (!e || !out || max <= 0) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    // results handed out by the previous poll are dead now: recycle their slots
+    for (auto& s : e->slots)
+        if (s.state == Slot::HANDED) s.state = Slot::FREE;
+    const auto t_end = Clock::now() + std::chrono::microseconds(timeout_us > 0 ? timeout_us : 0);
+    int got = 0;
+    const int nc = (int)e->model.n_classes;
+    for (;;) {
+        while (got < max && !e->fifo.empty()) {
+            Slot& s = e->slots[e->fifo.front()];
+            if (s.state == Slot::INFLIGHT) {
+                cudaError_t q = cudaEventQuery(s.done);
+                if (q == cudaErrorNotReady) break;
+                if (q != cudaSuccess) {
+                    s.status = SIB_ECUDA;
+                    set_error(std::string("batch failed: ") + cudaGetErrorString(q));
+                }
+                s.state = Slot::READY;
+                if (e->cfg.precision == SIB_PREC_BF16 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.h_guard_n[0];
+            }
+            while (got < max && s.next_entry < s.entries.size()) {
+                const Entry& en = s.entries[s.next_entry++];
+                sib_result& r = out[got++];
+                r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status; r.reserved = 0;
+                r.probs = s.h_probs + (size_t)en.offset * nc;
+                r.argmax = s.h_argmax + en.offset;
+            }
+            if (s.next_entry == s.entries.size()) {
+                s.state = Slot::HANDED;
+                e->fifo.pop_front();
+            } else {
+                break;
+            }
+        }
+        if (got > 0 || timeout_us == 0) break;
+        const bool pending = !e->fifo.empty() || (e->filling >= 0 && e->slots[e->filling].images > 0);
+        if (!pending) break;
+        if (timeout_us > 0 && Clock::now() >= t_end) break;
+        if (!e->fifo.empty()) {
+            // wait for the oldest batch without holding the lock
+            cudaEvent_t ev = e->slots[e->fifo.front()].done;
+            lk.unlock();
+            if (timeout_us < 0) {
+                cudaEventSynchronize(ev);
+            } else {
+                while (cudaEventQuery(ev) == cudaErrorNotReady && Clock::now() < t_end) std::this_thread::yield();
+            }
+            lk.lock();
+        } else if (timeout_us < 0) {
+            e->cv.wait(lk);  // the deadline thread will launch the filling slot
+        } else {
+            e->cv.wait_until(lk, t_end);
+        }
+    }
+    return got;
+}
+
+extern "C" long sib_format_json(const sib_result* r, char* buf, size_t cap) {
+    if (!r || !buf || !r->probs) return SIB_EINVAL;
+    return json_encode(r->probs, r->n, r->n_classes, buf, cap);
+}
+
+extern "C" int sib_stats_get(sib_engine* e, sib_stats* out) {
+    if (!e || !out) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    *out = e->stats;
+    return SIB_OK;
+}
+
+extern "C" int sib_forward_sync(sib_engine* e, const float* x, int n, float* probs, float* logits, int32_t* argmax) {
+    if (!e || !x || !probs || n < 0) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->sync_mu);
+    cudaSetDevice(e->device);
+    Slot& s = e->sync_slot;
+    const size_t img = e->model.img_elems, nc = e->model.n_classes;
+    std::vector<float> lg_host;
+    for (int done = 0; done < n;) {
+        const int b = std::min(n - done, e->cfg.max_batch);
+        std::memcpy(s.h_in, x + (size_t)done * img, (size_t)b * img * sizeof(float));
+        CU_TRY(cudaMemcpyAsync(s.dev.d_in, s.h_in, (size_t)b * img * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+        int r = e->run_forward(s.dev.d_in, b, s.dev.d_probs, logits ? s.dev.d_logits : nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
+        if (r) return r;
+        CU_TRY(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)b * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        CU_TRY(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)b * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        if (logits) CU_TRY(cudaMemcpyAsync(logits + (size_t)done * nc, s.dev.d_logits, (size_t)b * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
+        CU_TRY(cudaStreamSynchronize(s.stream));
+        std::memcpy(probs + (size_t)done * nc, s.h_probs, (size_t)b * nc * sizeof(float));
+        if (argmax) std::memcpy(argmax + done, s.h_argmax, (size_t)b * sizeof(int32_t));
+        done += b;
+    }
+    return SIB_OK;
+}
+
+extern "C" int sib_forward_device(sib_engine* e, const float* d_nhwc, int n, float* d_probs, float* d_logits,
+                                  int32_t* d_argmax, void* stream) {
+    if (!e || !d_nhwc || !d_probs || n < 0) return SIB_EINVAL;
+    if (n > e->cfg.max_batch) { set_error("n exceeds max_batch"); return SIB_ECAP; }
+    if (e->cfg.precision == SIB_PREC_BF16 && e->cfg.guard && !d_argmax) {
+        set_error("the guarded BF16 path needs d_argmax");
+        return SIB_EINVAL;
+    }
+    cudaSetDevice(e->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : e->sync_slot.stream;
+    return e->run_forward(d_nhwc, n, d_probs, d_logits, d_argmax, &e->dev_scratch.guard, st);
+}

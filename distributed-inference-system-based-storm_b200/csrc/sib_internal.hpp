@@ -1,0 +1,75 @@
+// sib_internal.hpp -- shared declarations inside libsib.so (not part of the C ABI).
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/sib.h"
+
+namespace sib {
+
+constexpr uint32_t kKindConv = 1;   // conv(kh,kw) VALID s1 + bias + ReLU + maxpool 2x2/2
+constexpr uint32_t kKindDense = 2;  // x.W + b (+ReLU when flags&1)
+constexpr int kMaxLayers = 16;
+constexpr int kMaxClasses = 32;
+
+struct LayerDesc {
+    uint32_t kind, a, b, c, d, flags, w_off, b_off;  // conv: a=kh b=kw c=cin d=cout; dense: a=in b=out
+};
+
+// Parsed model blob: stands where the reference keeps model/saved_model.pb (InferenceBolt.java:49).
+struct ModelDesc {
+    uint32_t in_h = 0, in_w = 0, in_c = 0, n_layers = 0, n_classes = 0, n_weights = 0;
+    LayerDesc layer[kMaxLayers]{};
+    std::vector<float> weights;
+    uint32_t img_elems = 0;
+    uint32_t max_store_act = 0;  // largest activation kept between layers (input, pooled maps, dense outputs)
+    int64_t flops_per_image = 0;
+    int preset = -1;  // 0 mnist-lenet5, 1 cifar-lenet5, 2 mnist-wide, 3 cifar-wide, -1 = other shape
+};
+
+int parse_model(const void* blob, size_t n, ModelDesc* out, std::string* err);
+
+void set_error(const std::string& s);
+
+// ---- codec (sib_json.cpp)
+long json_decode(const char* utf8, size_t len, float* out, long cap, int64_t dims[4]);
+long json_encode(const float* probs, long n, int n_classes, char* buf, size_t cap);
+int float_to_string(float x, char* buf);
+
+// ---- device side (sib_kernels_*.cu)
+struct DeviceLayer {
+    uint32_t kind, a, b, c, d, flags, w_off, b_off;
+};
+struct DeviceModel {
+    uint32_t in_h, in_w, in_c, n_layers, n_classes, img_elems, max_store_act, pad;
+    DeviceLayer layer[kMaxLayers];
+    const float* weights;  // device pointer, fp32, blob order
+};
+
+// fp32 CUDA-core forward. d_idx (may be null): run only images d_idx[0..n) (guard recompute), writing in place.
+// Any of d_logits/d_argmax/d_margin may be null. Returns cudaError_t as int.
+int launch_forward_fp32(const DeviceModel& m, const float* d_in, int n, const int32_t* d_idx, const int32_t* d_count,
+                        float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin, void* stream);
+int fp32_smem_bytes(const DeviceModel& m);
+
+// BF16 tensor-core whole-network kernel (sib_kernels_bf16.cu). Scratch for the margin guard: per-image top1-top2
+// logit margin, the compacted list of images below tau, and its length.
+struct GuardScratch {
+    float* d_margin = nullptr;
+    int32_t* d_list = nullptr;
+    int32_t* d_count = nullptr;
+};
+struct Bf16Weights {
+    void* d_packed = nullptr;  // weights pre-swizzled into mma fragment order, BF16, + fp32 biases
+    size_t bytes = 0;
+    int preset = -1;
+};
+bool bf16_supported(const ModelDesc& m);
+int bf16_prepare(const ModelDesc& m, Bf16Weights* out);  // uploads to the current device
+void bf16_release(Bf16Weights* w);
+int launch_forward_bf16(const Bf16Weights& w, const DeviceModel& m, const float* d_in, int n, float* d_probs,
+                        float* d_logits, int32_t* d_argmax, GuardScratch* guard, float tau, void* stream);
+
+}  // namespace sib

@@ -1,0 +1,137 @@
+/*
+ * sib.h -- C ABI of libsib.so: the B200-native replacement for the InferenceBolt hot path of
+ * HyoJong-Moon/Distributed-Inference-System-based-Storm.
+ *
+ * Every entry point is what a JNI / Panama binding of the reference's bolt would bind (INTEGRATION.md shows
+ * the Java side).  Plain pointers and sizes only; no C++ or torch types; no exception crosses this boundary.
+ * All functions return 0 / a non-negative count on success and a negative SIB_E* code on failure;
+ * sib_last_error() gives text for the calling thread's last failure.
+ *
+ * Reference citations are relative to /root/reference/src/main/java/dke/model/.
+ */
+#ifndef SIB_H
+#define SIB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes ------------------------------------------------------------------------------------- */
+#define SIB_OK 0
+#define SIB_EJSON (-1)   /* malformed JSON / unknown property: the reference catches JsonProcessingException,
+                            emits a null message and acks (InferenceBolt.java:92-99) */
+#define SIB_ESHAPE (-2)  /* ragged / wrong rank / wrong HxWxC / missing instances: the reference throws out of
+                            execute() (Tensor.create / copyTo IllegalArgumentException, InferenceBolt.java:80,86) */
+#define SIB_ECAP (-3)    /* caller buffer too small / tuple larger than max_batch */
+#define SIB_EAGAIN (-4)  /* every batch slot is busy: call sib_poll() and retry */
+#define SIB_EINVAL (-5)  /* bad argument / bad model blob */
+#define SIB_ECUDA (-6)   /* CUDA runtime failure, or no usable GPU (there is NO CPU fallback) */
+#define SIB_ECLOSED (-7) /* engine is shutting down */
+
+/* ---- precision of the forward pass -------------------------------------------------------------------- */
+#define SIB_PREC_BF16 0 /* tensor-core path: BF16 operands, fp32 accumulate (+ fp32 margin guard) */
+#define SIB_PREC_FP32 2 /* CUDA-core fp32 path (also the guard's recompute path) */
+
+typedef struct sib_engine sib_engine;
+
+/* Engine configuration. Zero / negative fields take the defaults noted. Read from the Storm conf Map that
+ * prepare() receives (InferenceBolt.java:44) so the topology CLI keeps its 3 arguments (MainTopology.java:36-38). */
+typedef struct sib_config {
+    int32_t device;      /* CUDA ordinal; <0 = task_index % device_count  (MainTopology.java:62 shuffle grouping
+                            x parallelism hint is the multi-GPU sharding; no collective) */
+    int32_t task_index;  /* TopologyContext.getThisTaskIndex() of this executor (InferenceBolt.java:44) */
+    int32_t max_batch;   /* images per micro-batch, flush-by-size              (default 4096) */
+    int32_t deadline_us; /* age of the oldest queued tuple that forces a flush (default 200)  */
+    int32_t precision;   /* SIB_PREC_*                                          (default BF16) */
+    int32_t n_slots;     /* pinned batch slots in the ring, >= 2               (default 4)    */
+    int32_t guard;       /* 1 = recompute low-margin images in fp32 so argmax equals the fp32 path (default 1) */
+    float guard_tau;     /* top1-top2 logit margin below which the guard recomputes (default 0.05) */
+} sib_config;
+
+/* One completed tuple. probs/argmax are engine-owned and stay valid until the next sib_poll() on the engine. */
+typedef struct sib_result {
+    uint64_t tag;          /* caller's tuple handle, returned untouched */
+    int32_t n;             /* images in the tuple (rows of predictions) */
+    int32_t n_classes;     /* columns of predictions (10 for the reference: InferenceBolt.java:86) */
+    int32_t status;        /* SIB_OK or SIB_ECUDA */
+    int32_t reserved;
+    const float *probs;    /* n x n_classes softmax probabilities, "output/Softmax:0" (InferenceBolt.java:83) */
+    const int32_t *argmax; /* n predicted classes (first maximum) */
+} sib_result;
+
+typedef struct sib_stats {
+    uint64_t tuples, images, batches;
+    uint64_t flush_by_size, flush_by_deadline, flush_explicit;
+    uint64_t guard_recomputed; /* images the margin guard re-ran in fp32 */
+    uint64_t batch_hist[16];   /* batch sizes, bucket b counts batches with 2^b <= images < 2^(b+1) */
+    uint64_t h2d_bytes, d2h_bytes;
+    uint64_t kernel_launches;
+} sib_stats;
+
+typedef struct sib_model_info {
+    int32_t in_h, in_w, in_c, n_layers, n_classes, n_weights;
+    int64_t flops_per_image; /* 2 * sum(M*N*K) over conv/dense layers */
+    int64_t bytes_per_image; /* H*W*C*4 in + n_classes*4 out */
+} sib_model_info;
+
+/* ---- life cycle: replaces InferenceBolt.prepare()'s SavedModelBundle.load / session (InferenceBolt.java:43-62) */
+int sib_device_count(void);
+int sib_model_describe(const void *model_blob, size_t n, sib_model_info *out);
+int sib_engine_open(const void *model_blob, size_t n, const sib_config *cfg, sib_engine **out);
+int sib_engine_close(sib_engine *e); /* flushes, waits for in-flight batches, frees everything */
+int sib_engine_info(sib_engine *e, sib_model_info *out, sib_config *effective_cfg);
+
+/* ---- per-tuple path: replaces the body of InferenceBolt.execute() (InferenceBolt.java:69-100) --------- */
+
+/* readValue(inputJson, InstObj.class) + Tensor.create(data) (InferenceBolt.java:76-80): decodes
+ * {"instances":[N][H][W][C]} straight into the pinned batch slot. Returns N (>0) or a negative code:
+ * SIB_EJSON => caller emits a null message and acks; SIB_ESHAPE => caller throws IllegalArgumentException. */
+int sib_submit_json(sib_engine *e, uint64_t tag, const char *utf8, size_t len);
+
+/* Same, for a caller that already holds fp32 NHWC (benchmarks; a TensorFlow-Java style caller). Input is copied
+ * before return. */
+int sib_submit_f32(sib_engine *e, uint64_t tag, const float *nhwc, int n);
+
+/* sess.runner().feed().fetch().run() + copyTo (InferenceBolt.java:81-86), decoupled: returns up to max completed
+ * tuples in submission order. timeout_us: 0 = don't wait, <0 = wait until at least one is ready or nothing is
+ * pending. Returns the count. Invalidates pointers handed out by the previous poll. */
+int sib_poll(sib_engine *e, sib_result *out, int max, int timeout_us);
+
+/* Launch the partially filled batch now (bolt cleanup(), tests). */
+int sib_flush(sib_engine *e);
+
+/* new ObjectMapper().writeValueAsString(predObj) (InferenceBolt.java:89-91, PredObj.java:8-17):
+ * {"predictions":[[p0,..,p9],..]} with java.lang.Float.toString number text. Returns length (no NUL) or SIB_ECAP. */
+long sib_format_json(const sib_result *r, char *buf, size_t cap);
+
+int sib_stats_get(sib_engine *e, sib_stats *out);
+
+/* ---- whole-batch synchronous forms (tests, benchmarks, oracle diff) ----------------------------------- */
+
+/* Host buffers in, host buffers out: H2D + forward + D2H on the engine's stream, then waits.
+ * probs: n x n_classes; logits (may be NULL): n x n_classes; argmax (may be NULL): n. */
+int sib_forward_sync(sib_engine *e, const float *nhwc_host, int n, float *probs, float *logits, int32_t *argmax);
+
+/* Device-resident form (kernel-level timing): pointers are CUDA device pointers on the engine's device, stream is
+ * a cudaStream_t (NULL = engine stream). Asynchronous. d_logits / d_argmax may be NULL. Needs n <= max_batch. */
+int sib_forward_device(sib_engine *e, const float *d_nhwc, int n, float *d_probs, float *d_logits,
+                       int32_t *d_argmax, void *stream);
+
+/* ---- stand-alone codec (same code the engine uses) ---------------------------------------------------- */
+
+/* Jackson semantics: number text -> double -> (float). dims receives {N,H,W,C}. Returns float count or code. */
+long sib_json_decode(const char *utf8, size_t len, float *out, long cap, int64_t dims[4]);
+long sib_json_encode(const float *probs, long n, int n_classes, char *buf, size_t cap);
+int sib_float_to_string(float x, char *buf24); /* java.lang.Float.toString; returns length */
+
+const char *sib_last_error(void);
+const char *sib_strerror(int code);
+const char *sib_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SIB_H */

@@ -1,0 +1,109 @@
+"""The micro-batcher through the C ABI: tags and order, flush-by-size, flush-by-deadline, JSON submit, back-pressure.
+Mirrors what InferenceBolt.execute() promises per tuple (InferenceBolt.java:69-100)."""
+import time
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _drain(e, want, timeout_s=10.0):
+    out = []
+    t0 = time.time()
+    while len(out) < want and time.time() - t0 < timeout_s:
+        out += e.poll(timeout_us=100000)
+    return out
+
+
+def test_submit_poll_order_and_values(sib, oracle, presets):
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 21, 300)
+    _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=1000, n_slots=3) as e:
+        got = []
+        for i in range(300):
+            while True:
+                rc = e.submit_f32(1000 + i, x[i])
+                if rc == sib.native.EAGAIN:
+                    got += e.poll(timeout_us=1000)
+                    continue
+                assert rc == 1
+                break
+        e.flush()
+        got += _drain(e, 300 - len(got))
+        assert [t for t, *_ in got] == list(range(1000, 1300))       # submission order, exactly once
+        for i, (_, p, a, status) in enumerate(got):
+            assert status == 0 and p.shape == (1, 10)
+            assert np.abs(p[0] - pr[i]).max() <= 1e-5
+            assert a[0] == pr[i].argmax()
+        s = e.stats()
+        assert s.tuples == 300 and s.images == 300
+        assert s.flush_by_size == 4 and s.batches >= 5                 # 4 x 64 + remainder
+        assert s.h2d_bytes == 300 * m.img_elems * 4
+
+
+def test_flush_by_deadline(sib, presets):
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 22, 3)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=4096, deadline_us=2000) as e:
+        t0 = time.time()
+        for i in range(3):
+            assert e.submit_f32(i, x[i]) == 1
+        got = _drain(e, 3, timeout_s=5.0)                                # no flush() call: the deadline thread launches
+        dt = time.time() - t0
+        assert [t for t, *_ in got] == [0, 1, 2]
+        assert dt < 2.0
+        s = e.stats()
+        assert s.flush_by_deadline == 1 and s.flush_by_size == 0 and s.flush_explicit == 0
+        assert s.batch_hist[1] == 1                                      # one batch of 3 images: bucket [2,4)
+
+
+def test_multi_image_tuples_and_json_submit(sib, oracle, presets):
+    m = presets["cifar-lenet5"]
+    ms = sib.modelspec
+    x = ms.synthetic_images(m, 23, 5)
+    _, pr = oracle.Model(m.to_blob()).forward(x)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=8, deadline_us=500) as e:
+        assert e.submit_json(7, ms.instances_json(x[:2])) == 2           # N=2 rows in one tuple (InstObj.java:8)
+        assert e.submit_f32(8, x[2:5]) == 3
+        assert e.submit_json(9, b'{"instances": [[[[1.0]]]') == sib.native.EJSON
+        assert e.submit_json(9, b'{"instances": [[[[1.0]]]]}') == sib.native.ESHAPE   # 1x1x1 is not 32x32x3
+        assert e.submit_json(9, ms.instances_json(np.zeros((9, 32, 32, 3), np.float32))) == sib.native.ECAP
+        e.flush()
+        got = _drain(e, 2)
+        assert [(t, p.shape) for t, p, *_ in got] == [(7, (2, 10)), (8, (3, 10))]
+        assert np.abs(got[0][1] - pr[:2]).max() <= 1e-5
+        assert np.abs(got[1][1] - pr[2:]).max() <= 1e-5
+        # library-side formatting equals the oracle's PredObj text for the same probabilities
+        assert e.submit_json(10, ms.instances_json(x[:1])) == 1
+        e.flush()
+        msgs = []
+        t0 = time.time()
+        while not msgs and time.time() - t0 < 5:
+            msgs = e.poll_json(timeout_us=100000)
+        tag, text = msgs[0]
+        assert tag == 10 and text.startswith(b'{"predictions":[[') and text.endswith(b"]]}")
+        vals = np.array(eval(text.decode().replace("E", "e"))["predictions"], np.float32)
+        assert np.abs(vals - pr[:1]).max() <= 1e-5
+
+
+def test_back_pressure_is_eagain_not_deadlock(sib, presets):
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 24, 1)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=2, deadline_us=10**6, n_slots=2) as e:
+        rcs = [e.submit_f32(i, x[0]) for i in range(6)]
+        assert rcs[:4] == [1, 1, 1, 1] and sib.native.EAGAIN in rcs[4:]   # 2 slots x 2 images, nobody polled
+        got = _drain(e, 4)
+        assert [t for t, *_ in got] == [0, 1, 2, 3]
+        e.poll()                                                           # hands the slots back
+        assert e.submit_f32(99, x[0]) == 1
+
+
+def test_close_with_pending_work(sib, presets):
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 25, 10)
+    e = sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6)
+    for i in range(10):
+        e.submit_f32(i, x[i])
+    e.close()  # must flush, wait and free without hanging
