@@ -186,7 +186,7 @@ def run_ours(args):
     prec_name = args.precision
     if prec_name == "auto":
         prec_name = sib.default_bench_precision()
-    prec = {"fp32": native.PREC_FP32, "bf16": native.PREC_BF16, "fp16": getattr(native, "PREC_FP16", 1)}[prec_name]
+    prec = {"fp32": native.PREC_FP32, "bf16": native.PREC_BF16, "fp16": native.PREC_FP16}[prec_name]
     B = args.batch
     eng = native.Engine(blob, device=dev, task_index=rank, max_batch=B, deadline_us=200, precision=prec,
                         n_slots=4, guard=not args.no_guard)
@@ -198,7 +198,8 @@ def run_ours(args):
     d_in = [torch.from_numpy(h).cuda() for h in host_batches]
     d_probs = torch.empty((B, nc), dtype=torch.float32, device="cuda")
     d_argmax = torch.empty((B,), dtype=torch.int32, device="cuda")
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()  # a real (non-null) stream: kernels and timing events share it
+    stream.wait_stream(torch.cuda.current_stream())
 
     def step(i):
         eng.forward_device(d_in[i % R].data_ptr(), B, d_probs.data_ptr(), 0, d_argmax.data_ptr(), stream.cuda_stream)
@@ -227,6 +228,7 @@ def run_ours(args):
     step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     units, secs = sharding.aggregate(B * args.steps, t0_local, dist if world > 1 else None)
     value = units / secs
+    torch.cuda.current_stream().wait_stream(stream)
     checksum = float(d_probs.sum().item())  # every row sums to 1: B
     assert abs(checksum - B) < 1e-2 * B, checksum
 

@@ -13,9 +13,9 @@ from .bolt import InferenceBolt, OutputCollector, Tuple  # noqa: F401
 
 def smoke_precisions():
     """(precision, max-abs probability tolerance) pairs the smoke run covers."""
-    return [(native.PREC_FP32, 1e-5)]
+    return [(native.PREC_FP32, 1e-5), (native.PREC_FP16, 1e-2)]
 
 
 def default_bench_precision() -> str:
     """Precision bench.py uses when none is given: the fastest path that is parity-green."""
-    return "fp32"
+    return "fp16"

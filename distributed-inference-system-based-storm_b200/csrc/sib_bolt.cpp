@@ -32,7 +32,7 @@ void InferenceBolt::prepare(const Conf& conf, const TopologyContext& ctx, Output
     auto tau = conf.find("sib.guard.tau");
     cfg.guard_tau = tau == conf.end() ? 0.0f : (float)std::atof(tau->second.c_str());
     auto pr = conf.find("sib.precision");
-    cfg.precision = (pr != conf.end() && pr->second == "fp32") ? SIB_PREC_FP32 : SIB_PREC_BF16;
+    cfg.precision = pr == conf.end() ? SIB_PREC_FP16 : pr->second == "fp32" ? SIB_PREC_FP32 : pr->second == "bf16" ? SIB_PREC_BF16 : SIB_PREC_FP16;
     int rc = sib_engine_open(blob_.data(), blob_.size(), &cfg, &engine_);
     // the reference lets SavedModelBundle.load throw out of prepare(); so do we
     if (rc != SIB_OK) throw std::runtime_error(std::string("InferenceBolt.prepare: ") + sib_last_error());

@@ -75,7 +75,7 @@ struct sib_engine {
     sib_config cfg{};
     int device = 0;
     float* d_weights = nullptr;
-    Bf16Weights bf16{};
+    TcWeights tc{};
     std::vector<Slot> slots;
     int filling = -1;
     std::deque<int> fifo;  // launched slots, submission order
@@ -107,7 +107,7 @@ int sib_engine::alloc_dev(DevBufs& d, bool with_io) {
         CU_TRY(cudaMalloc((void**)&d.d_logits, mb * nc * sizeof(float)));
         CU_TRY(cudaMalloc((void**)&d.d_argmax, mb * sizeof(int32_t)));
     }
-    if (cfg.precision == SIB_PREC_BF16) {
+    if (cfg.precision != SIB_PREC_FP32) {
         CU_TRY(cudaMalloc((void**)&d.guard.d_margin, mb * sizeof(float)));
         CU_TRY(cudaMalloc((void**)&d.guard.d_list, mb * sizeof(int32_t)));
         CU_TRY(cudaMalloc((void**)&d.guard.d_count, 2 * sizeof(int32_t)));
@@ -146,7 +146,8 @@ void sib_engine::free_slot(Slot& s) {
     s = Slot{};
 }
 
-// One forward pass on device-resident data. BF16: tensor-core kernel, then the fp32 guard over low-margin images.
+// One forward pass on device-resident data. FP16/BF16: tensor-core kernel, then the fp32 guard over the
+// low-margin images it listed (same stream, so the list and its count are ready).
 int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
                             GuardScratch* g, cudaStream_t st) {
     int e;
@@ -155,7 +156,7 @@ int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_l
         stats.kernel_launches += 1;
     } else {
         const bool guard = cfg.guard != 0;
-        e = launch_forward_bf16(bf16, dm, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, st);
+        e = launch_forward_tc(tc, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, nullptr, st);
         stats.kernel_launches += 1;
         if (!e && guard) {
             e = launch_forward_fp32(dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, nullptr, st);
@@ -186,7 +187,7 @@ int sib_engine::launch_locked(int si, int reason) {
     chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)s.images * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream), "D2H probs");
     chk(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)s.images * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H argmax");
     size_t d2h = (size_t)s.images * (nc * sizeof(float) + sizeof(int32_t));
-    if (cfg.precision == SIB_PREC_BF16 && cfg.guard) {
+    if (cfg.precision != SIB_PREC_FP32 && cfg.guard) {
         chk(cudaMemcpyAsync(s.h_guard_n, s.dev.guard.d_count, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H guard count");
         d2h += sizeof(int32_t);
     }
@@ -262,12 +263,13 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     if (c.max_batch <= 0) c.max_batch = 4096;
     if (c.deadline_us <= 0) c.deadline_us = 200;
     if (c.n_slots < 2) c.n_slots = 4;
-    if (c.guard_tau <= 0.0f) c.guard_tau = 0.05f;
-    if (c.precision != SIB_PREC_BF16 && c.precision != SIB_PREC_FP32) {
-        set_error("precision must be SIB_PREC_BF16 or SIB_PREC_FP32");
+    if (c.precision != SIB_PREC_FP16 && c.precision != SIB_PREC_BF16 && c.precision != SIB_PREC_FP32) {
+        set_error("precision must be SIB_PREC_FP16, SIB_PREC_BF16 or SIB_PREC_FP32");
         delete e;
         return SIB_EINVAL;
     }
+    // guard threshold: a bit over twice the largest logit error seen for the operand type (DESIGN.md "margin guard")
+    if (c.guard_tau <= 0.0f) c.guard_tau = c.precision == SIB_PREC_BF16 ? 0.30f : 0.05f;
     int ndev = sib_device_count();
     if (ndev <= 0) {
         set_error("no CUDA device visible: libsib has no CPU fallback");
@@ -276,8 +278,8 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     }
     if (c.device < 0) c.device = (c.task_index < 0 ? 0 : c.task_index) % ndev;  // executor -> GPU, MainTopology.java:62
     if (c.device >= ndev) { set_error("device ordinal out of range"); delete e; return SIB_EINVAL; }
-    if (c.precision == SIB_PREC_BF16 && !bf16_supported(e->model)) {
-        set_error("SIB_PREC_BF16 covers the LeNet-5 presets (mnist-lenet5, cifar-lenet5); open this model with SIB_PREC_FP32");
+    if (c.precision != SIB_PREC_FP32 && !tc_supported(e->model)) {
+        set_error("the tensor-core precisions cover the LeNet-5 presets (mnist-lenet5, cifar-lenet5); open this model with SIB_PREC_FP32");
         delete e;
         return SIB_EINVAL;
     }
@@ -297,8 +299,8 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     std::memcpy(dm.layer, m.layer, sizeof(LayerDesc) * kMaxLayers);
     dm.weights = e->d_weights;
     if (fp32_smem_bytes(dm) > 227 * 1024) { set_error("model activations exceed shared memory"); return fail(SIB_EINVAL); }
-    if (c.precision == SIB_PREC_BF16) {
-        r = bf16_prepare(m, &e->bf16);
+    if (c.precision != SIB_PREC_FP32) {
+        r = tc_prepare(m, c.precision, &e->tc);
         if (r) return fail(r);
     }
     e->slots.resize(c.n_slots);
@@ -324,7 +326,7 @@ extern "C" int sib_engine_close(sib_engine* e) {
     for (auto& s : e->slots) e->free_slot(s);
     e->free_slot(e->sync_slot);
     e->free_dev(e->dev_scratch);
-    bf16_release(&e->bf16);
+    tc_release(&e->tc);
     cudaFree(e->d_weights);
     delete e;
     return SIB_OK;
@@ -449,7 +451,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                     set_error(std::string("batch failed: ") + cudaGetErrorString(q));
                 }
                 s.state = Slot::READY;
-                if (e->cfg.precision == SIB_PREC_BF16 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.h_guard_n[0];
+                if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.h_guard_n[0];
             }
             while (got < max && s.next_entry < s.entries.size()) {
                 const Entry& en = s.entries[s.next_entry++];
@@ -528,11 +530,34 @@ extern "C" int sib_forward_device(sib_engine* e, const float* d_nhwc, int n, flo
                                   int32_t* d_argmax, void* stream) {
     if (!e || !d_nhwc || !d_probs || n < 0) return SIB_EINVAL;
     if (n > e->cfg.max_batch) { set_error("n exceeds max_batch"); return SIB_ECAP; }
-    if (e->cfg.precision == SIB_PREC_BF16 && e->cfg.guard && !d_argmax) {
-        set_error("the guarded BF16 path needs d_argmax");
+    if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard && !d_argmax) {
+        set_error("the guarded tensor-core path needs d_argmax");
         return SIB_EINVAL;
     }
     cudaSetDevice(e->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : e->sync_slot.stream;
+    cudaStream_t st = (cudaStream_t)stream;  // NULL is the CUDA default stream, as everywhere in CUDA
     return e->run_forward(d_nhwc, n, d_probs, d_logits, d_argmax, &e->dev_scratch.guard, st);
+}
+
+// Test hook: runs the tensor-core kernel on up to 16 host images and returns the intermediate activations of the
+// first 16-image tile (pooled conv1 map of both 8-image slots, pooled conv2 features, fc1 output), as fp32.
+// TF exposes the same thing by fetching inner tensors (Session.runner().fetch(name), InferenceBolt.java:81-85).
+extern "C" long sib_debug_stage_dump(sib_engine* e, const float* x, int n, float* out, long cap) {
+    if (!e || !x || !out || n <= 0 || n > 16) return SIB_EINVAL;
+    if (e->cfg.precision == SIB_PREC_FP32) { set_error("stage dump needs a tensor-core precision"); return SIB_EINVAL; }
+    const long need = (long)tc_debug_floats(e->model.preset);
+    if (cap < need) return SIB_ECAP;
+    std::unique_lock<std::mutex> lk(e->sync_mu);
+    cudaSetDevice(e->device);
+    Slot& s = e->sync_slot;
+    float* d_dbg = nullptr;
+    CU_TRY(cudaMalloc((void**)&d_dbg, need * sizeof(float)));
+    CU_TRY(cudaMemset(d_dbg, 0, need * sizeof(float)));
+    CU_TRY(cudaMemcpy(s.dev.d_in, x, (size_t)n * e->model.img_elems * sizeof(float), cudaMemcpyHostToDevice));
+    int r = launch_forward_tc(e->tc, s.dev.d_in, n, s.dev.d_probs, nullptr, s.dev.d_argmax, nullptr, 0.f, d_dbg, s.stream);
+    cudaError_t ce = cudaStreamSynchronize(s.stream);
+    if (!r && ce == cudaSuccess) ce = cudaMemcpy(out, d_dbg, need * sizeof(float), cudaMemcpyDeviceToHost);
+    cudaFree(d_dbg);
+    if (r || ce != cudaSuccess) { set_error(std::string("stage dump: ") + cudaGetErrorString(r ? (cudaError_t)r : ce)); return SIB_ECUDA; }
+    return need;
 }

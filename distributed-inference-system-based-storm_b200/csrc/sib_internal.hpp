@@ -54,22 +54,24 @@ int launch_forward_fp32(const DeviceModel& m, const float* d_in, int n, const in
                         float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin, void* stream);
 int fp32_smem_bytes(const DeviceModel& m);
 
-// BF16 tensor-core whole-network kernel (sib_kernels_bf16.cu). Scratch for the margin guard: per-image top1-top2
-// logit margin, the compacted list of images below tau, and its length.
+// Tensor-core whole-network kernel (sib_kernels_tc.cu). Scratch for the margin guard: per-image top1-top2 logit
+// margin, the compacted list of images below tau, and its length.
 struct GuardScratch {
     float* d_margin = nullptr;
     int32_t* d_list = nullptr;
     int32_t* d_count = nullptr;
 };
-struct Bf16Weights {
-    void* d_packed = nullptr;  // weights pre-swizzled into mma fragment order, BF16, + fp32 biases
+struct TcWeights {
+    void* d_packed = nullptr;  // weights pre-swizzled into mma fragment order (half or bf16) + fp32 biases
     size_t bytes = 0;
     int preset = -1;
+    int precision = SIB_PREC_FP16;
 };
-bool bf16_supported(const ModelDesc& m);
-int bf16_prepare(const ModelDesc& m, Bf16Weights* out);  // uploads to the current device
-void bf16_release(Bf16Weights* w);
-int launch_forward_bf16(const Bf16Weights& w, const DeviceModel& m, const float* d_in, int n, float* d_probs,
-                        float* d_logits, int32_t* d_argmax, GuardScratch* guard, float tau, void* stream);
+bool tc_supported(const ModelDesc& m);
+int tc_prepare(const ModelDesc& m, int precision, TcWeights* out);  // uploads to the current device
+void tc_release(TcWeights* w);
+size_t tc_debug_floats(int preset);
+int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
+                      GuardScratch* guard, float tau, float* d_dbg, void* stream);
 
 }  // namespace sib

@@ -196,15 +196,15 @@ int fp32_smem_bytes(const DeviceModel& m) { return (int)(2u * kImgs * m.max_stor
 int launch_forward_fp32(const DeviceModel& m, const float* d_in, int n, const int32_t* d_idx, const int32_t* d_count,
                         float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin, void* stream) {
     if (n <= 0) return 0;
-    static thread_local int configured_for = -1;
+    static int configured_for[64] = {};
     int smem = fp32_smem_bytes(m);
-    if (configured_for < smem) {
-        cudaError_t e = cudaFuncSetAttribute(forward_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return (int)e;
-        configured_for = smem;
-    }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
+    if (configured_for[dev & 63] < smem) {  // function attributes are per device
+        cudaError_t e = cudaFuncSetAttribute(forward_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return (int)e;
+        configured_for[dev & 63] = smem;
+    }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int ctas = (n + kImgs - 1) / kImgs;
     int per_sm = smem > 0 ? max(1, min(8, (227 * 1024) / (smem + 1024))) : 8;

@@ -1,0 +1,704 @@
+// sib_kernels_tc.cu -- persistent whole-network tensor-core kernel for the LeNet-5 presets (sm_100a).
+//
+// Replaces Session.run("input:0" -> "output/Softmax:0") (InferenceBolt.java:81-85) for the graded models
+// (conv5x5(6) -> pool -> conv5x5(16) -> pool -> 120 -> 84 -> 10 -> softmax; 28x28x1 and 32x32x3).
+//
+// Shape of the kernel (DESIGN.md "tensor-core kernel" has the numbers behind each choice):
+//   * one persistent CTA per SM; every fc weight lives in shared memory as pre-swizzled mma B fragments for the
+//     whole launch, conv weights live in registers of the warps that use them;
+//   * warps are specialised and pipelined through shared-memory rings with mbarriers, 8 images per ring slot:
+//       conv1 warps: stream fp32 NHWC rows from HBM (128-bit coalesced loads, 8 rows in flight per warp),
+//                    convert to half precision into a 2-row private staging ring, build im2col A fragments with a
+//                    5-row sliding register window (each staged row is read once and feeds 5 kernel rows),
+//                    mma.sync m16n8k16, bias+ReLU+2x2 maxpool fused in registers (even/odd column tiles make the
+//                    pool thread-local), pooled rows -> p1 ring;
+//       conv2 warps: same sliding window over p1 rows, N=16, pool thread-local by tile-row permutation -> p2 ring;
+//       fc warps   : 16-image M tiles: 400(256)->120->84->10, bias+ReLU fused, then a quad-shuffle softmax /
+//                    argmax / top1-top2 margin, and the margin guard's compaction list.
+//   * why mma.sync and not tcgen05 here: the contractions are N=6 and N=16 wide with K=75/150; the im2col operand
+//     cannot be described to a tcgen05 shared-memory descriptor without materialising it (5-25x the bytes), and
+//     shared-memory operand bandwidth, not MMA issue, is then the limiter. Register-resident sliding windows avoid
+//     the expansion. Measured mma.sync m16n8k16 rate on this B200: 557 TFLOP/s (profiles/microbench_r01.jsonl).
+//
+// Operand type is a template parameter: __half (default: 11-bit significand, max logit error 2e-2 on the presets)
+// or __nv_bfloat16 (8-bit significand, ~1e-1). Accumulation is always fp32.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <vector>
+
+#include "sib_internal.hpp"
+
+namespace sib {
+namespace {
+
+constexpr int kConv1Warps = 8;
+constexpr int kConv2Warps = 4;
+constexpr int kFcWarps = 4;
+constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps;
+constexpr int kThreadsTc = kWarps * 32;
+constexpr int kG = 8;     // images per ring slot (conv stages)
+constexpr int kPair = 16; // images per fc M tile = 2 slots
+
+template <int H_, int W_, int C_>
+struct Net {
+    static constexpr int H = H_, W = W_, C = C_;
+    static constexpr int OH1 = H - 4, OW1 = W - 4, PH1 = OH1 / 2, PW1 = OW1 / 2;
+    static constexpr int OH2 = PH1 - 4, OW2 = PW1 - 4, PH2 = OH2 / 2, PW2 = OW2 / 2;
+    static constexpr int C1 = 6, C2 = 16, F1 = 120, F2 = 84, F3 = 10;
+    static constexpr int IMG = H * W * C;
+    static constexpr int ROWF = W * C;              // floats per image row
+    static constexpr int K1ROW = 5 * C;             // real K per kernel row of conv1 (<= 15)
+    static constexpr int SPANS = kG * OW1 / 32;     // conv1 work items per slot: 32 output columns x all rows
+    static constexpr int TILES2 = kG * OW2 / 16;    // conv2 M tiles per slot
+    static constexpr int ITEMS2 = TILES2 * 2;       // x 2 N tiles
+    static constexpr int FEAT = PH2 * PW2 * C2;     // 400 | 256
+    static constexpr int KS1 = FEAT / 16;
+    static constexpr int P1_ROW = PW1 * C1, P1_IMG = PH1 * P1_ROW;  // halves
+    static constexpr int P1_BUF = kG * P1_IMG + 16;                 // + slack for the K-padding over-read
+    static constexpr int P2_STRIDE = FEAT + 8;                      // halves; +8 keeps A-fragment loads conflict-free
+    static constexpr int P2_BUF = kPair * P2_STRIDE;
+    static constexpr int H1_STRIDE = 136, H2_STRIDE = 104;
+    static constexpr int PD = (H % 8 == 0) ? 8 : 7;                 // rows in flight per conv1 warp
+    static constexpr int NCHUNK = (40 * C + 3) / 4;                 // 16-byte chunks per staged span row
+    static constexpr int RING_ROW = ((40 * C + 16 + 7) / 8) * 8;    // halves per staged row incl. zero slack
+    static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && H % PD == 0, "tiling");
+    static_assert(K1ROW <= 15 && NCHUNK <= 32 && OW1 % 2 == 0 && OW2 % 2 == 0 && W % 4 == 0 && ROWF % 4 == 0, "layout");
+    // packed weight image (32-bit words)
+    static constexpr int W_C1 = 0;                               // [2 variants][5 kh][32 lanes][2]
+    static constexpr int W_C2 = W_C1 + 2 * 5 * 64;               // [5 kh][2 ks][2 nt][32][2]
+    static constexpr int W_F1 = W_C2 + 5 * 2 * 2 * 64;           // [KS1][16 nt][32][2]
+    static constexpr int W_F2 = W_F1 + KS1 * 16 * 64;            // [8 ks][12 nt][32][2]
+    static constexpr int W_F3 = W_F2 + 8 * 12 * 64;              // [6 ks][2 nt][32][2]
+    static constexpr int W_BIAS = W_F3 + 6 * 2 * 64;             // fp32: c1[8] c2[16] f1[128] f2[96] f3[16]
+    static constexpr int W_TOTAL = W_BIAS + 8 + 16 + 128 + 96 + 16;
+    // shared memory map (bytes)
+    static constexpr int S_FCW = 0;                                        // fc1|fc2|fc3 fragments
+    static constexpr int S_FCW_BYTES = (W_BIAS - W_F1) * 4;
+    static constexpr int S_BIAS = S_FCW + S_FCW_BYTES;                     // 264 floats
+    static constexpr int S_P1 = S_BIAS + 264 * 4;
+    static constexpr int S_P2 = S_P1 + 2 * P1_BUF * 2;
+    static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
+    static constexpr int S_H2 = S_H1 + kPair * H1_STRIDE * 2;
+    static constexpr int S_RING = S_H2 + kPair * H2_STRIDE * 2;
+    static constexpr int S_BAR = S_RING + kConv1Warps * 2 * RING_ROW * 2;
+    static constexpr int S_TOTAL = S_BAR + 8 * 8;
+    static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_BAR % 8 == 0, "align");
+    static_assert(S_TOTAL <= 227 * 1024, "shared memory");
+};
+
+// ---- small PTX helpers --------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// Waits for the phase with the given parity to complete. A bounded spin: a protocol bug traps instead of hanging
+// the GPU (the trap surfaces as a launch failure on the host).
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0, spin = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+        if (ok) return;
+        if ((++spin & 1023u) == 0) {  // watchdog: ~2 s at 2 GHz
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ll) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void fc_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kFcWarps * 32) : "memory"); }
+
+template <typename T> struct Ops;
+template <> struct Ops<__half> {
+    __device__ static __forceinline__ uint32_t pack(float lo, float hi) {
+        __half2 h = __floats2half2_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    __device__ static __forceinline__ void mma(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+    }
+    static uint16_t host_bits(float x) { return __half_as_ushort(__float2half_rn(x)); }
+};
+template <> struct Ops<__nv_bfloat16> {
+    __device__ static __forceinline__ uint32_t pack(float lo, float hi) {
+        __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&h);
+    }
+    __device__ static __forceinline__ void mma(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+    }
+    static uint16_t host_bits(float x) { return __bfloat16_as_ushort(__float2bfloat16_rn(x)); }
+};
+
+__device__ __forceinline__ uint32_t lds32(const uint16_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+__device__ __forceinline__ float4 ldg_stream(const float* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+struct TcParams {
+    const uint32_t* wpack;
+    const float* in;
+    int n;
+    float* probs;
+    float* logits;   // may be null
+    int32_t* argmax; // may be null
+    float* margin;   // may be null
+    int32_t* list;   // guard compaction list (may be null)
+    int32_t* count;
+    float tau;
+    float* dbg;      // may be null: CTA 0 dumps p1/p2/h1/h2 of its first 16 images (tests)
+};
+
+// ---- conv1 role ---------------------------------------------------------------------------------------------
+
+template <typename N, typename T>
+__device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* smem, int cw, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    uint16_t* ring = reinterpret_cast<uint16_t*>(smem + N::S_RING) + cw * 2 * N::RING_ROW;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+    uint64_t* p1_full = bars + 0;   // [2]
+    uint64_t* p1_empty = bars + 2;  // [2]
+    // B fragments of conv1: even-column tiles and odd-column tiles (K shifted by one element so that odd columns
+    // read 4-byte aligned pairs from the staged row)
+    uint32_t bE[5][2], bO[5][2];
+#pragma unroll
+    for (int kh = 0; kh < 5; kh++) {
+        const uint2 e = *reinterpret_cast<const uint2*>(P.wpack + N::W_C1 + (0 * 5 + kh) * 64 + lane * 2);
+        const uint2 o = *reinterpret_cast<const uint2*>(P.wpack + N::W_C1 + (1 * 5 + kh) * 64 + lane * 2);
+        bE[kh][0] = e.x; bE[kh][1] = e.y; bO[kh][0] = o.x; bO[kh][1] = o.y;
+    }
+    const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS);
+    const float bias0 = biasp[2 * t], bias1 = biasp[2 * t + 1];
+
+    const int nPairs = (P.n + kPair - 1) / kPair;
+    // spans in CTA order: local slot lq = 0,1,2.. ; slot lq -> pair Qi = lq/2 (global pair blockIdx.x + Qi*gridDim.x)
+    auto span_src = [&](int gs, int& img0, bool& valid) {
+        const int lq = gs / N::SPANS;
+        const int pair = blockIdx.x + (lq >> 1) * gridDim.x;
+        valid = pair < nPairs;
+        img0 = pair * kPair + (lq & 1) * kG;
+    };
+    // per-lane source of the 16-byte chunk this lane stages for span s of a slot
+    auto chunk_ptr = [&](int img0, int s) -> const float* {
+        const int p0 = 32 * s;
+        const int u_start = (p0 / N::OW1) * N::W + p0 % N::OW1;
+        const int F0 = u_start * N::C + 4 * lane;
+        int img = img0 + F0 / N::ROWF;
+        img = min(img, P.n - 1);  // tail slots re-read the last image; their outputs are never written
+        return P.in + (size_t)img * N::IMG + F0 % N::ROWF;
+    };
+
+    float4 pre[N::PD];
+    int gs = cw;
+    int img0;
+    bool valid;
+    span_src(gs, img0, valid);
+    if (!valid) return;
+    const float* src = chunk_ptr(img0, gs % N::SPANS);
+#pragma unroll
+    for (int r = 0; r < N::PD; r++)
+        if (lane < N::NCHUNK) pre[r] = ldg_stream(src + r * N::ROWF);
+
+    while (valid) {
+        const int s = gs % N::SPANS, lq = gs / N::SPANS;
+        const int buf = lq & 1, use = lq >> 1;
+        uint16_t* p1 = reinterpret_cast<uint16_t*>(smem + N::S_P1) + buf * N::P1_BUF;
+        // next span (for the tail prefetch)
+        int n_img0;
+        bool n_valid;
+        span_src(gs + kConv1Warps, n_img0, n_valid);
+        const float* n_src = n_valid ? chunk_ptr(n_img0, (gs + kConv1Warps) % N::SPANS) : src;
+
+        // fragment offsets into a staged row (halves)
+        const int p0 = 32 * s;
+        const int u_start = (p0 / N::OW1) * N::W + p0 % N::OW1;
+        auto uoff = [&](int p) { return ((p / N::OW1) * N::W + p % N::OW1 - u_start) * N::C; };
+        const int offE0 = uoff(p0 + 2 * g) + 2 * t, offE1 = uoff(p0 + 2 * g + 16) + 2 * t;
+        const int offO0 = uoff(p0 + 2 * g + 1) - 1 + 2 * t, offO1 = uoff(p0 + 2 * g + 17) - 1 + 2 * t;
+        // pooled output columns of this lane
+        const int pp0 = 16 * s + g, pp1 = pp0 + 8;
+        const int o0 = (pp0 / N::PW1) * N::P1_IMG + (pp0 % N::PW1) * N::C1 + 2 * t;
+        const int o1 = (pp1 / N::PW1) * N::P1_IMG + (pp1 % N::PW1) * N::C1 + 2 * t;
+        const bool dump = P.dbg && blockIdx.x == 0 && lq < 2;
+
+        mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
+
+        uint32_t aE[5][4], aO[5][4];
+        float prev[4];
+#pragma unroll
+        for (int h = 0; h < N::H; h++) {
+            // stage row h: fp32 -> half, 8 bytes per lane
+            uint16_t* rr = ring + (h & 1) * N::RING_ROW;
+            if (lane < N::NCHUNK) {
+                const float4 v = pre[h % N::PD];
+                uint2 pk;
+                pk.x = Ops<T>::pack(v.x, v.y);
+                pk.y = Ops<T>::pack(v.z, v.w);
+                *reinterpret_cast<uint2*>(rr + 4 * lane) = pk;
+                // refill the slot: same span while rows remain, else the first rows of this warp's next span
+                if (h + N::PD < N::H) pre[h % N::PD] = ldg_stream(src + (h + N::PD) * N::ROWF);
+                else if (n_valid) pre[h % N::PD] = ldg_stream(n_src + (h + N::PD - N::H) * N::ROWF);
+            }
+            __syncwarp();
+            {
+                uint32_t(&e)[4] = aE[h % 5];
+                uint32_t(&o)[4] = aO[h % 5];
+                e[0] = lds32(rr + offE0); e[1] = lds32(rr + offE1); e[2] = lds32(rr + offE0 + 8); e[3] = lds32(rr + offE1 + 8);
+                o[0] = lds32(rr + offO0); o[1] = lds32(rr + offO1); o[2] = lds32(rr + offO0 + 8); o[3] = lds32(rr + offO1 + 8);
+            }
+            if (h >= 4) {
+                const int oh = h - 4;
+                float cE[4] = {0.f, 0.f, 0.f, 0.f}, cO[4] = {0.f, 0.f, 0.f, 0.f};
+                float dE[4] = {0.f, 0.f, 0.f, 0.f}, dO[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int kh = 0; kh < 5; kh++) {  // two accumulator chains per tile keep 4 mma in flight
+                    if (kh < 3) { Ops<T>::mma(cE, aE[(oh + kh) % 5], bE[kh]); Ops<T>::mma(cO, aO[(oh + kh) % 5], bO[kh]); }
+                    else        { Ops<T>::mma(dE, aE[(oh + kh) % 5], bE[kh]); Ops<T>::mma(dO, aO[(oh + kh) % 5], bO[kh]); }
+                }
+                float m[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) m[i] = fmaxf(cE[i] + dE[i], cO[i] + dO[i]);  // pool over the column pair
+                if ((oh & 1) == 0) {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) prev[i] = m[i];
+                } else {
+                    const int ph = oh >> 1;
+                    // relu(max(.)+b) == max over the window of relu(.+b)
+                    const float v0 = fmaxf(fmaxf(m[0], prev[0]) + bias0, 0.f), v1 = fmaxf(fmaxf(m[1], prev[1]) + bias1, 0.f);
+                    const float v2 = fmaxf(fmaxf(m[2], prev[2]) + bias0, 0.f), v3 = fmaxf(fmaxf(m[3], prev[3]) + bias1, 0.f);
+                    if (t < 3) {
+                        *reinterpret_cast<uint32_t*>(p1 + o0 + ph * N::P1_ROW) = Ops<T>::pack(v0, v1);
+                        *reinterpret_cast<uint32_t*>(p1 + o1 + ph * N::P1_ROW) = Ops<T>::pack(v2, v3);
+                        if (dump) {
+                            float* d = P.dbg + lq * kG * N::P1_IMG;
+                            d[o0 + ph * N::P1_ROW] = v0; d[o0 + ph * N::P1_ROW + 1] = v1;
+                            d[o1 + ph * N::P1_ROW] = v2; d[o1 + ph * N::P1_ROW + 1] = v3;
+                        }
+                    }
+                }
+            }
+        }
+        mbar_arrive(&p1_full[buf]);
+        gs += kConv1Warps;
+        valid = n_valid;
+        src = n_src;
+        img0 = n_img0;
+    }
+}
+
+// ---- conv2 role ---------------------------------------------------------------------------------------------
+
+template <typename N, typename T>
+__device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* smem, int w2, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+    uint64_t* p1_full = bars + 0;
+    uint64_t* p1_empty = bars + 2;
+    uint64_t* p2_full = bars + 4;
+    uint64_t* p2_empty = bars + 6;
+    const int nt = w2 & 1;  // items of one warp always share the N tile: item = tile*2 + nt, ITEMS2 is even
+    static_assert(N::ITEMS2 % 2 == 0 && kConv2Warps % 2 == 0, "nt must be constant per warp");
+    uint32_t bW[5][2][2];
+#pragma unroll
+    for (int kh = 0; kh < 5; kh++)
+#pragma unroll
+        for (int ks = 0; ks < 2; ks++) {
+            const uint2 v = *reinterpret_cast<const uint2*>(P.wpack + N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64 + lane * 2);
+            bW[kh][ks][0] = v.x; bW[kh][ks][1] = v.y;
+        }
+    const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS) + 8;
+    const float bias0 = biasp[nt * 8 + 2 * t], bias1 = biasp[nt * 8 + 2 * t + 1];
+    const int nPairs = (P.n + kPair - 1) / kPair;
+
+    for (int gi = w2;; gi += kConv2Warps) {
+        const int lq = gi / N::ITEMS2, item = gi % N::ITEMS2;
+        const int Qi = lq >> 1;
+        if ((int)(blockIdx.x + Qi * gridDim.x) >= nPairs) break;
+        const int tile = item >> 1;
+        const int buf1 = lq & 1, use1 = lq >> 1;
+        const int buf2 = Qi & 1, use2 = Qi >> 1;
+        const uint16_t* p1 = reinterpret_cast<const uint16_t*>(smem + N::S_P1) + buf1 * N::P1_BUF;
+        uint16_t* p2 = reinterpret_cast<uint16_t*>(smem + N::S_P2) + buf2 * N::P2_BUF;
+        // tile row r <-> output column P = 16*tile + 2*(r%8) + r/8: fragment rows g and g+8 are a pooling pair
+        const int Pe = 16 * tile + 2 * g;
+        const int imgl = Pe / N::OW2, ow = Pe % N::OW2;
+        const int offA0 = imgl * N::P1_IMG + ow * N::C1 + 2 * t;  // even column (rows g)
+        const int offA1 = offA0 + N::C1;                           // odd column  (rows g+8)
+        const int pw = ow >> 1;
+        const int o2 = ((lq & 1) * kG + imgl) * N::P2_STRIDE + pw * N::C2 + nt * 8 + 2 * t;
+        const bool dump = P.dbg && blockIdx.x == 0 && Qi == 0;
+
+        mbar_wait(&p1_full[buf1], use1 & 1);
+        mbar_wait(&p2_empty[buf2], (use2 & 1) ^ 1);
+
+        uint32_t a[5][2][4];
+        float prev0 = 0.f, prev1 = 0.f;
+#pragma unroll
+        for (int r = 0; r < N::PH1; r++) {
+            const uint16_t* row = p1 + r * N::P1_ROW;
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {
+                uint32_t(&f)[4] = a[r % 5][ks];
+                f[0] = lds32(row + offA0 + ks * 16);
+                f[1] = lds32(row + offA1 + ks * 16);
+                f[2] = lds32(row + offA0 + ks * 16 + 8);
+                f[3] = lds32(row + offA1 + ks * 16 + 8);
+            }
+            if (r >= 4) {
+                const int oh = r - 4;
+                float c[4] = {0.f, 0.f, 0.f, 0.f}, d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int kh = 0; kh < 5; kh++) {
+                    Ops<T>::mma(c, a[(oh + kh) % 5][0], bW[kh][0]);
+                    Ops<T>::mma(d, a[(oh + kh) % 5][1], bW[kh][1]);
+                }
+                const float h0 = fmaxf(c[0] + d[0], c[2] + d[2]), h1 = fmaxf(c[1] + d[1], c[3] + d[3]);
+                if ((oh & 1) == 0) {
+                    prev0 = h0; prev1 = h1;
+                } else {
+                    const int ph = oh >> 1;
+                    const float v0 = fmaxf(fmaxf(h0, prev0) + bias0, 0.f), v1 = fmaxf(fmaxf(h1, prev1) + bias1, 0.f);
+                    *reinterpret_cast<uint32_t*>(p2 + o2 + ph * N::PW2 * N::C2) = Ops<T>::pack(v0, v1);
+                    if (dump) {
+                        float* dd = P.dbg + 2 * kG * N::P1_IMG;
+                        dd[o2 + ph * N::PW2 * N::C2] = v0; dd[o2 + ph * N::PW2 * N::C2 + 1] = v1;
+                    }
+                }
+            }
+        }
+        mbar_arrive(&p1_empty[buf1]);
+        mbar_arrive(&p2_full[buf2]);
+    }
+}
+
+// ---- fc role ------------------------------------------------------------------------------------------------
+
+template <typename N, typename T>
+__device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, int fw, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+    uint64_t* p2_full = bars + 4;
+    uint64_t* p2_empty = bars + 6;
+    const uint32_t* w1 = reinterpret_cast<const uint32_t*>(smem + N::S_FCW);
+    const uint32_t* w2 = w1 + (N::W_F2 - N::W_F1);
+    const uint32_t* w3 = w1 + (N::W_F3 - N::W_F1);
+    const float* bias = reinterpret_cast<const float*>(smem + N::S_BIAS);  // c1[8] c2[16] f1[128] f2[96] f3[16]
+    uint16_t* h1 = reinterpret_cast<uint16_t*>(smem + N::S_H1);
+    uint16_t* h2 = reinterpret_cast<uint16_t*>(smem + N::S_H2);
+    const int nPairs = (P.n + kPair - 1) / kPair;
+
+    for (int Qi = 0;; Qi++) {
+        const int pair = blockIdx.x + Qi * gridDim.x;
+        if (pair >= nPairs) break;
+        const int buf = Qi & 1, use = Qi >> 1;
+        const uint16_t* p2 = reinterpret_cast<const uint16_t*>(smem + N::S_P2) + buf * N::P2_BUF;
+        const bool dump = P.dbg && blockIdx.x == 0 && Qi == 0;
+        mbar_wait(&p2_full[buf], use & 1);
+        // ---- fc1: [16 x FEAT] . [FEAT x 128], 4 N tiles per warp
+        {
+            float acc[4][4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            const uint16_t* a0p = p2 + g * N::P2_STRIDE + 2 * t;
+            const uint16_t* a1p = a0p + 8 * N::P2_STRIDE;
+#pragma unroll 5
+            for (int ks = 0; ks < N::KS1; ks++) {
+                uint32_t a[4];
+                a[0] = lds32(a0p + ks * 16); a[1] = lds32(a1p + ks * 16); a[2] = lds32(a0p + ks * 16 + 8); a[3] = lds32(a1p + ks * 16 + 8);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint2 bv = *reinterpret_cast<const uint2*>(w1 + (ks * 16 + fw * 4 + j) * 64 + lane * 2);
+                    const uint32_t b[2] = {bv.x, bv.y};
+                    Ops<T>::mma(acc[j], a, b);
+                }
+            }
+            mbar_arrive(&p2_empty[buf]);  // p2 fully consumed by this lane
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int n0 = (fw * 4 + j) * 8 + 2 * t;
+                const float b0 = bias[24 + n0], b1 = bias[24 + n0 + 1];
+                const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
+                const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
+                *reinterpret_cast<uint32_t*>(h1 + g * N::H1_STRIDE + n0) = Ops<T>::pack(v0, v1);
+                *reinterpret_cast<uint32_t*>(h1 + (g + 8) * N::H1_STRIDE + n0) = Ops<T>::pack(v2, v3);
+                if (dump) {
+                    float* d = P.dbg + 2 * kG * N::P1_IMG + N::P2_BUF;
+                    d[g * 128 + n0] = v0; d[g * 128 + n0 + 1] = v1; d[(g + 8) * 128 + n0] = v2; d[(g + 8) * 128 + n0 + 1] = v3;
+                }
+            }
+        }
+        fc_bar();
+        // ---- fc2: [16 x 128] . [128 x 96], 3 N tiles per warp
+        {
+            float acc[3][4];
+#pragma unroll
+            for (int j = 0; j < 3; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            const uint16_t* a0p = h1 + g * N::H1_STRIDE + 2 * t;
+            const uint16_t* a1p = a0p + 8 * N::H1_STRIDE;
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) {
+                uint32_t a[4];
+                a[0] = lds32(a0p + ks * 16); a[1] = lds32(a1p + ks * 16); a[2] = lds32(a0p + ks * 16 + 8); a[3] = lds32(a1p + ks * 16 + 8);
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    const uint2 bv = *reinterpret_cast<const uint2*>(w2 + (ks * 12 + fw * 3 + j) * 64 + lane * 2);
+                    const uint32_t b[2] = {bv.x, bv.y};
+                    Ops<T>::mma(acc[j], a, b);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const int n0 = (fw * 3 + j) * 8 + 2 * t;
+                const float b0 = bias[152 + n0], b1 = bias[152 + n0 + 1];
+                const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
+                const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
+                *reinterpret_cast<uint32_t*>(h2 + g * N::H2_STRIDE + n0) = Ops<T>::pack(v0, v1);
+                *reinterpret_cast<uint32_t*>(h2 + (g + 8) * N::H2_STRIDE + n0) = Ops<T>::pack(v2, v3);
+            }
+        }
+        fc_bar();
+        // ---- fc3 + softmax/argmax/margin: one warp; the others start the next pair's fc1 meanwhile
+        if (fw == 0) {
+            float acc[2][4];
+#pragma unroll
+            for (int j = 0; j < 2; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            const uint16_t* a0p = h2 + g * N::H2_STRIDE + 2 * t;
+            const uint16_t* a1p = a0p + 8 * N::H2_STRIDE;
+#pragma unroll
+            for (int ks = 0; ks < 6; ks++) {
+                uint32_t a[4];
+                a[0] = lds32(a0p + ks * 16); a[1] = lds32(a1p + ks * 16); a[2] = lds32(a0p + ks * 16 + 8); a[3] = lds32(a1p + ks * 16 + 8);
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const uint2 bv = *reinterpret_cast<const uint2*>(w3 + (ks * 2 + j) * 64 + lane * 2);
+                    const uint32_t b[2] = {bv.x, bv.y};
+                    Ops<T>::mma(acc[j], a, b);
+                }
+            }
+            // lane (g,t) holds, for image g (half 0) and g+8 (half 1): classes 2t,2t+1 and, when t==0, 8,9
+#pragma unroll
+            for (int hrow = 0; hrow < 2; hrow++) {
+                const int img = pair * kPair + g + hrow * 8;
+                float x[4];
+                x[0] = acc[0][hrow * 2 + 0] + bias[248 + 2 * t];
+                x[1] = acc[0][hrow * 2 + 1] + bias[248 + 2 * t + 1];
+                x[2] = t == 0 ? acc[1][hrow * 2 + 0] + bias[248 + 8] : -INFINITY;
+                x[3] = t == 0 ? acc[1][hrow * 2 + 1] + bias[248 + 9] : -INFINITY;
+                const int cls[4] = {2 * t, 2 * t + 1, 8, 9};
+                float mx = x[0];
+                int am = cls[0];
+#pragma unroll
+                for (int i = 1; i < 4; i++)
+                    if (x[i] > mx) { mx = x[i]; am = cls[i]; }  // ascending class order within the lane except 8,9
+                // quad reduction with first-maximum tie-break on the class index
+#pragma unroll
+                for (int o = 1; o <= 2; o <<= 1) {
+                    const float ox = __shfl_xor_sync(0xffffffffu, mx, o);
+                    const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+                    if (ox > mx || (ox == mx && oa < am)) { mx = ox; am = oa; }
+                }
+                float second = -INFINITY;
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (cls[i] != am || (i >= 2 && t != 0)) second = fmaxf(second, x[i]);
+                second = fmaxf(second, __shfl_xor_sync(0xffffffffu, second, 1));
+                second = fmaxf(second, __shfl_xor_sync(0xffffffffu, second, 2));
+                float e[4], s = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; i++) { e[i] = expf(x[i] - mx); s += e[i]; }  // exp(-inf) = 0 for the unused slots
+                s += __shfl_xor_sync(0xffffffffu, s, 1);
+                s += __shfl_xor_sync(0xffffffffu, s, 2);
+                if (img < P.n) {
+                    float* pr = P.probs + (size_t)img * 10;
+                    *reinterpret_cast<float2*>(pr + 2 * t) = make_float2(e[0] / s, e[1] / s);
+                    if (t == 0) *reinterpret_cast<float2*>(pr + 8) = make_float2(e[2] / s, e[3] / s);
+                    if (P.logits) {
+                        float* lg = P.logits + (size_t)img * 10;
+                        *reinterpret_cast<float2*>(lg + 2 * t) = make_float2(x[0], x[1]);
+                        if (t == 0) *reinterpret_cast<float2*>(lg + 8) = make_float2(x[2], x[3]);
+                    }
+                    if (t == 0) {
+                        if (P.argmax) P.argmax[img] = am;
+                        const float mg = mx - second;
+                        if (P.margin) P.margin[img] = mg;
+                        if (P.list && mg < P.tau) P.list[atomicAdd(P.count, 1)] = img;  // guard: recompute in fp32
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <typename N, typename T>
+__global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // ---- one-time set-up: fc weight fragments + biases into shared memory, zero the rings, init barriers
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(P.wpack + N::W_F1);
+        uint4* dst = reinterpret_cast<uint4*>(smem + N::S_FCW);
+        for (int i = threadIdx.x; i < N::S_FCW_BYTES / 16; i += blockDim.x) dst[i] = src[i];
+        float* b = reinterpret_cast<float*>(smem + N::S_BIAS);
+        for (int i = threadIdx.x; i < 264; i += blockDim.x) b[i] = reinterpret_cast<const float*>(P.wpack + N::W_BIAS)[i];
+        uint32_t* z = reinterpret_cast<uint32_t*>(smem + N::S_P1);
+        for (int i = threadIdx.x; i < (N::S_BAR - N::S_P1) / 4; i += blockDim.x) z[i] = 0u;  // p1,p2,h1,h2,rings
+        if (threadIdx.x == 0) {
+            uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+            for (int i = 0; i < 2; i++) {
+                mbar_init(&bars[0 + i], N::SPANS * 32);               // p1_full : every lane of every span
+                mbar_init(&bars[2 + i], N::ITEMS2 * 32);              // p1_empty: every lane of every conv2 item
+                mbar_init(&bars[4 + i], 2 * N::ITEMS2 * 32);          // p2_full : two slots of conv2 items
+                mbar_init(&bars[6 + i], kFcWarps * 32);               // p2_empty: every fc lane
+            }
+        }
+    }
+    __syncthreads();
+    if (warp < kConv1Warps) conv1_role<N, T>(P, smem, warp, lane);
+    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T>(P, smem, warp - kConv1Warps, lane);
+    else fc_role<N, T>(P, smem, warp - kConv1Warps - kConv2Warps, lane);
+}
+
+// ---- host side: weight packing ----------------------------------------------------------------------------------
+
+// B fragment of mma.m16n8k16 (col layout): lane (g = lane/4, t = lane%4) holds {B[2t][g], B[2t+1][g]} and
+// {B[2t+8][g], B[2t+9][g]}; `at(k, n)` returns the fp32 weight or 0 outside the real matrix.
+template <typename T, typename F>
+void pack_b(uint32_t* dst, F at) {
+    for (int lane = 0; lane < 32; lane++) {
+        const int g = lane >> 2, t = lane & 3;
+        for (int r = 0; r < 2; r++) {
+            const int k = 2 * t + 8 * r;
+            const uint32_t lo = Ops<T>::host_bits(at(k, g)), hi = Ops<T>::host_bits(at(k + 1, g));
+            dst[lane * 2 + r] = lo | (hi << 16);
+        }
+    }
+}
+
+template <typename N, typename T>
+std::vector<uint32_t> pack_weights(const ModelDesc& m) {
+    std::vector<uint32_t> w(N::W_TOTAL, 0u);
+    const float* wt = m.weights.data();
+    const LayerDesc* L = m.layer;
+    const float* f1 = wt + L[0].w_off;  // [5][5][C][6]
+    for (int v = 0; v < 2; v++)
+        for (int kh = 0; kh < 5; kh++)
+            pack_b<T>(&w[N::W_C1 + (v * 5 + kh) * 64], [&](int k, int n) -> float {
+                const int j = k - v;  // odd-column tiles read one element earlier, so their K is shifted by one
+                if (j < 0 || j >= N::K1ROW || n >= N::C1) return 0.f;
+                return f1[((kh * 5 + j / N::C) * N::C + j % N::C) * N::C1 + n];
+            });
+    const float* f2 = wt + L[1].w_off;  // [5][5][6][16]
+    for (int kh = 0; kh < 5; kh++)
+        for (int ks = 0; ks < 2; ks++)
+            for (int nt = 0; nt < 2; nt++)
+                pack_b<T>(&w[N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64], [&](int k, int n) -> float {
+                    const int j = ks * 16 + k;
+                    if (j >= 5 * N::C1) return 0.f;
+                    return f2[((kh * 5 + j / N::C1) * N::C1 + j % N::C1) * N::C2 + nt * 8 + n];
+                });
+    auto dense = [&](int off, int ksteps, int ntiles, const LayerDesc& D) {
+        const float* k = wt + D.w_off;  // [in][out]
+        for (int ks = 0; ks < ksteps; ks++)
+            for (int nt = 0; nt < ntiles; nt++)
+                pack_b<T>(&w[off + (ks * ntiles + nt) * 64], [&](int kk, int n) -> float {
+                    const int i = ks * 16 + kk, j = nt * 8 + n;
+                    return (i < (int)D.a && j < (int)D.b) ? k[i * D.b + j] : 0.f;
+                });
+    };
+    dense(N::W_F1, N::KS1, 16, L[2]);
+    dense(N::W_F2, 8, 12, L[3]);
+    dense(N::W_F3, 6, 2, L[4]);
+    float* b = reinterpret_cast<float*>(&w[N::W_BIAS]);
+    std::memcpy(b, wt + L[0].b_off, 6 * 4);
+    std::memcpy(b + 8, wt + L[1].b_off, 16 * 4);
+    std::memcpy(b + 24, wt + L[2].b_off, 120 * 4);
+    std::memcpy(b + 152, wt + L[3].b_off, 84 * 4);
+    std::memcpy(b + 248, wt + L[4].b_off, 10 * 4);
+    return w;
+}
+
+template <typename N, typename T>
+int launch(const TcWeights& w, const TcParams& p, cudaStream_t st) {
+    static bool configured[64] = {};
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {  // function attributes are per device
+        cudaError_t e = cudaFuncSetAttribute(forward_tc_kernel<N, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, N::S_TOTAL);
+        if (e != cudaSuccess) return (int)e;
+        configured[dev & 63] = true;
+    }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int pairs = (p.n + kPair - 1) / kPair;
+    const int grid = pairs < sms ? pairs : sms;
+    forward_tc_kernel<N, T><<<grid, kThreadsTc, N::S_TOTAL, st>>>(p);
+    return (int)cudaGetLastError();
+}
+
+using NetMnist = Net<28, 28, 1>;
+using NetCifar = Net<32, 32, 3>;
+
+}  // namespace
+
+bool tc_supported(const ModelDesc& m) { return m.preset == 0 || m.preset == 1; }
+
+int tc_prepare(const ModelDesc& m, int precision, TcWeights* out) {
+    if (!tc_supported(m)) { set_error("tensor-core path covers the LeNet-5 presets only"); return SIB_EINVAL; }
+    std::vector<uint32_t> w;
+    const bool bf = precision == SIB_PREC_BF16;
+    if (m.preset == 0) w = bf ? pack_weights<NetMnist, __nv_bfloat16>(m) : pack_weights<NetMnist, __half>(m);
+    else w = bf ? pack_weights<NetCifar, __nv_bfloat16>(m) : pack_weights<NetCifar, __half>(m);
+    out->bytes = w.size() * 4;
+    out->preset = m.preset;
+    out->precision = precision;
+    if (cudaMalloc(&out->d_packed, out->bytes) != cudaSuccess ||
+        cudaMemcpy(out->d_packed, w.data(), out->bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("tensor-core weight upload failed");
+        return SIB_ECUDA;
+    }
+    return SIB_OK;
+}
+
+void tc_release(TcWeights* w) {
+    if (w && w->d_packed) cudaFree(w->d_packed);
+    if (w) *w = TcWeights{};
+}
+
+size_t tc_debug_floats(int preset) {
+    return preset == 0 ? 2 * kG * NetMnist::P1_IMG + NetMnist::P2_BUF + 16 * 128
+                       : 2 * kG * NetCifar::P1_IMG + NetCifar::P2_BUF + 16 * 128;
+}
+
+int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
+                      GuardScratch* guard, float tau, float* d_dbg, void* stream) {
+    if (n <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    TcParams p{};
+    p.wpack = static_cast<const uint32_t*>(w.d_packed);
+    p.in = d_in; p.n = n; p.probs = d_probs; p.logits = d_logits; p.argmax = d_argmax;
+    p.tau = tau; p.dbg = d_dbg;
+    if (guard) {
+        p.margin = guard->d_margin; p.list = guard->d_list; p.count = guard->d_count;
+        cudaError_t e = cudaMemsetAsync(guard->d_count, 0, sizeof(int32_t), st);  // the list starts empty every launch
+        if (e != cudaSuccess) return (int)e;
+    }
+    const bool bf = w.precision == SIB_PREC_BF16;
+    if (w.preset == 0) return bf ? launch<NetMnist, __nv_bfloat16>(w, p, st) : launch<NetMnist, __half>(w, p, st);
+    return bf ? launch<NetCifar, __nv_bfloat16>(w, p, st) : launch<NetCifar, __half>(w, p, st);
+}
+
+}  // namespace sib

@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsib.so")
 
 OK, EJSON, ESHAPE, ECAP, EAGAIN, EINVAL, ECUDA, ECLOSED = 0, -1, -2, -3, -4, -5, -6, -7
-PREC_BF16, PREC_FP32 = 0, 2
+PREC_FP16, PREC_BF16, PREC_FP32 = 0, 1, 2
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(f"{LIB_PATH} is not built: run `python __graft_entry__.py build` (nvcc, sm_100a). "
@@ -59,6 +59,7 @@ SYMBOLS = {
     "sib_stats_get": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "sib_forward_sync": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sib_forward_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sib_debug_stage_dump": (C.c_long, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_long]),
     "sib_json_decode": (C.c_long, [C.c_char_p, C.c_size_t, C.c_void_p, C.c_long, C.POINTER(C.c_int64)]),
     "sib_json_encode": (C.c_long, [C.c_void_p, C.c_long, C.c_int, C.c_char_p, C.c_size_t]),
     "sib_float_to_string": (C.c_int, [C.c_float, C.c_char_p]),
@@ -131,7 +132,7 @@ class Engine:
     """One engine = one executor's model replica on one GPU (InferenceBolt.prepare(), InferenceBolt.java:43-62)."""
 
     def __init__(self, blob: bytes, device: int = -1, task_index: int = 0, max_batch: int = 4096,
-                 deadline_us: int = 200, precision: int = PREC_BF16, n_slots: int = 4, guard: bool = True,
+                 deadline_us: int = 200, precision: int = PREC_FP16, n_slots: int = 4, guard: bool = True,
                  guard_tau: float = 0.0):
         self._h = C.c_void_p()
         self._blob = blob
@@ -227,6 +228,14 @@ class Engine:
         if rc:
             raise SibError(rc, "sib_forward_sync")
         return probs, logits, argmax
+
+    def stage_dump(self, x: np.ndarray) -> np.ndarray:
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros(1 << 16, np.float32)
+        r = lib.sib_debug_stage_dump(self._h, _p(x), x.size // self.img_elems, _p(out), out.size)
+        if r < 0:
+            raise SibError(int(r), "sib_debug_stage_dump")
+        return out[:r]
 
     def forward_device(self, d_in: int, n: int, d_probs: int, d_logits: int = 0, d_argmax: int = 0, stream: int = 0):
         rc = lib.sib_forward_device(self._h, C.c_void_p(d_in), n, C.c_void_p(d_probs), C.c_void_p(d_logits or None),

@@ -32,8 +32,11 @@ extern "C" {
 #define SIB_ECLOSED (-7) /* engine is shutting down */
 
 /* ---- precision of the forward pass -------------------------------------------------------------------- */
-#define SIB_PREC_BF16 0 /* tensor-core path: BF16 operands, fp32 accumulate (+ fp32 margin guard) */
-#define SIB_PREC_FP32 2 /* CUDA-core fp32 path (also the guard's recompute path) */
+#define SIB_PREC_FP16 0 /* tensor-core path, half operands (11-bit significand), fp32 accumulate, fp32 margin guard.
+                           Default: same tensor rate as BF16 with 8x smaller logit error; inputs are in [0,1) and
+                           activations of these nets stay far below 65504 */
+#define SIB_PREC_BF16 1 /* tensor-core path, bfloat16 operands (8-bit significand, fp32 range), fp32 accumulate, guard */
+#define SIB_PREC_FP32 2 /* CUDA-core fp32 path (any model the blob can describe; also the guard's recompute path) */
 
 typedef struct sib_engine sib_engine;
 
@@ -45,10 +48,10 @@ typedef struct sib_config {
     int32_t task_index;  /* TopologyContext.getThisTaskIndex() of this executor (InferenceBolt.java:44) */
     int32_t max_batch;   /* images per micro-batch, flush-by-size              (default 4096) */
     int32_t deadline_us; /* age of the oldest queued tuple that forces a flush (default 200)  */
-    int32_t precision;   /* SIB_PREC_*                                          (default BF16) */
+    int32_t precision;   /* SIB_PREC_*                                          (default FP16) */
     int32_t n_slots;     /* pinned batch slots in the ring, >= 2               (default 4)    */
     int32_t guard;       /* 1 = recompute low-margin images in fp32 so argmax equals the fp32 path (default 1) */
-    float guard_tau;     /* top1-top2 logit margin below which the guard recomputes (default 0.05) */
+    float guard_tau;     /* top1-top2 logit margin below which the guard recomputes (default 0.05 FP16, 0.30 BF16) */
 } sib_config;
 
 /* One completed tuple. probs/argmax are engine-owned and stay valid until the next sib_poll() on the engine. */
@@ -116,9 +119,13 @@ int sib_stats_get(sib_engine *e, sib_stats *out);
 int sib_forward_sync(sib_engine *e, const float *nhwc_host, int n, float *probs, float *logits, int32_t *argmax);
 
 /* Device-resident form (kernel-level timing): pointers are CUDA device pointers on the engine's device, stream is
- * a cudaStream_t (NULL = engine stream). Asynchronous. d_logits / d_argmax may be NULL. Needs n <= max_batch. */
+ * a cudaStream_t (NULL = the CUDA default stream). Asynchronous: the work is only ordered on that stream. d_logits / d_argmax may be NULL. Needs n <= max_batch. */
 int sib_forward_device(sib_engine *e, const float *d_nhwc, int n, float *d_probs, float *d_logits,
                        int32_t *d_argmax, void *stream);
+
+/* Test hook: intermediate activations of the tensor-core kernel for the first 16-image tile, fp32 (what fetching
+ * inner tensors of the TF graph would give, InferenceBolt.java:81-85). Returns floats written or a code. */
+long sib_debug_stage_dump(sib_engine *e, const float *nhwc_host, int n, float *out, long cap);
 
 /* ---- stand-alone codec (same code the engine uses) ---------------------------------------------------- */
 

@@ -21,7 +21,7 @@ typedef struct sib_harness sib_harness;
 #define SIB_EV_ACK 2  /* OutputCollector.ack(tuple)                 InferenceBolt.java:99 */
 
 /* conf: "key=value\n" lines standing in for the Storm conf Map of prepare() (InferenceBolt.java:44). Keys:
- * sib.max.batch, sib.deadline.us, sib.precision (bf16|fp32), sib.device, sib.slots, sib.guard, sib.guard.tau.
+ * sib.max.batch, sib.deadline.us, sib.precision (fp16|bf16|fp32), sib.device, sib.slots, sib.guard, sib.guard.tau.
  * task_index: TopologyContext.getThisTaskIndex(). Runs new InferenceBolt() + prepare(). */
 int sib_harness_open(const void *model_blob, size_t n, const char *conf, int task_index, sib_harness **out);
 /* execute(tuple) with tuple.getString(0) = utf8. Returns 0, or SIB_ESHAPE when execute() threw the

@@ -1,0 +1,152 @@
+"""The tensor-core whole-network kernel (SIB_PREC_FP16 / SIB_PREC_BF16) against the CPU oracle.
+
+Stated tolerances (DESIGN.md "precision"): the operands are rounded to 11 (fp16) or 8 (bf16) significant bits, the
+accumulation is fp32, logits of the D2 nets reach |x| ~ 12:
+    fp16: logits max-abs <= 5e-2, probabilities <= 1e-2        bf16: logits <= 0.30, probabilities <= 8e-2
+argmax must equal the fp32 oracle's for every image (the margin guard recomputes near-ties in fp32 on the GPU),
+except where the fp64 shadow oracle shows a genuine tie (< 1e-5)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp16": (5e-2, 1e-2), "bf16": (0.30, 8e-2)}
+
+
+def _prec(sib, name):
+    return {"fp16": sib.native.PREC_FP16, "bf16": sib.native.PREC_BF16}[name]
+
+
+def _stages(oracle, m, x):
+    """pooled conv1 map, pooled conv2 features and fc1 output per image, from the oracle's single ops."""
+    L = m.layers
+    w = m.weights
+    p1s, p2s, h1s = [], [], []
+    for img in x:
+        a = oracle.conv2d_valid(img, w[L[0].w_off:L[0].w_off + 25 * m.c * 6].reshape(5, 5, m.c, 6)) + w[L[0].b_off:L[0].b_off + 6]
+        p1 = oracle.maxpool2(np.maximum(a, 0))
+        b = oracle.conv2d_valid(p1, w[L[1].w_off:L[1].w_off + 25 * 6 * 16].reshape(5, 5, 6, 16)) + w[L[1].b_off:L[1].b_off + 16]
+        p2 = oracle.maxpool2(np.maximum(b, 0))
+        h1 = np.maximum(oracle.dense(p2.reshape(-1), w[L[2].w_off:L[2].w_off + L[2].a * 120].reshape(L[2].a, 120)) + w[L[2].b_off:L[2].b_off + 120], 0)
+        p1s.append(p1); p2s.append(p2.reshape(-1)); h1s.append(h1)
+    return np.stack(p1s), np.stack(p2s), np.stack(h1s)
+
+
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+def test_stage_dump_matches_oracle_stages(sib, oracle, presets, name):
+    """Localises a kernel bug to conv1 / conv2 / fc1 (TF would let you fetch these tensors by name)."""
+    m = presets[name]
+    x = sib.modelspec.synthetic_images(m, 61, 16, kind="patches")
+    p1, p2, h1 = _stages(oracle, m, x)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=64, guard=False) as e:
+        d = e.stage_dump(x)
+    n1 = p1[0].size
+    got_p1 = d[:16 * n1].reshape(16, *p1.shape[1:])
+    feat = p2.shape[1]
+    got_p2 = d[16 * n1:16 * n1 + 16 * (feat + 8)].reshape(16, feat + 8)[:, :feat]
+    got_h1 = d[16 * n1 + 16 * (feat + 8):].reshape(16, 128)[:, :120]
+    assert np.abs(got_p1 - p1).max() <= 4e-3 * max(1.0, np.abs(p1).max()), "conv1+pool stage"
+    assert np.abs(got_p2 - p2).max() <= 6e-3 * max(1.0, np.abs(p2).max()), "conv2+pool stage"
+    assert np.abs(got_h1 - h1).max() <= 8e-3 * max(1.0, np.abs(h1).max()), "fc1 stage"
+
+
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+@pytest.mark.parametrize("prec", ["fp16", "bf16"])
+@pytest.mark.parametrize("kind", ["uniform", "patches"])
+def test_tc_path_matches_oracle(sib, oracle, presets, name, prec, kind):
+    m = presets[name]
+    n = 1000  # not a multiple of 16: last tile is ragged
+    x = sib.modelspec.synthetic_images(m, 62, n, kind=kind)
+    om = oracle.Model(m.to_blob())
+    lg, pr = om.forward(x, threads=0)
+    tl, tp = TOL[prec]
+    with sib.native.Engine(m.to_blob(), precision=_prec(sib, prec), max_batch=512, guard=False) as e:  # 1000 > 512
+        gp, gl, ga = e.forward_sync(x)
+    assert np.isfinite(gl).all()
+    assert np.abs(gl - lg).max() <= tl, float(np.abs(gl - lg).max())
+    assert np.abs(gp - pr).max() <= tp, float(np.abs(gp - pr).max())
+    np.testing.assert_allclose(gp.sum(1), 1.0, atol=1e-5)
+    assert (ga == gl.argmax(1)).all()                      # the kernel's argmax is the argmax of its own logits
+    # unguarded flips may only happen where the fp32 margin is inside the error band
+    s = np.sort(lg, 1)
+    flips = ga != lg.argmax(1)
+    assert (s[flips, -1] - s[flips, -2] < 2 * tl).all()
+
+
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+@pytest.mark.parametrize("prec", ["fp16", "bf16"])
+def test_guard_makes_argmax_exact(sib, oracle, presets, name, prec):
+    m = presets[name]
+    n = 4096
+    x = sib.modelspec.synthetic_images(m, 63, n)
+    om = oracle.Model(m.to_blob())
+    lg, pr = om.forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), precision=_prec(sib, prec), max_batch=n, guard=True) as e:
+        gp, gl, ga = e.forward_sync(x)
+        tau = float(e.cfg.guard_tau)
+    bad = np.nonzero(ga != lg.argmax(1))[0]
+    if len(bad):
+        lg64, _ = om.forward64(x[bad])
+        s = np.sort(lg64, 1)
+        assert (s[:, -1] - s[:, -2] < 1e-5).all(), (bad, s[:, -1] - s[:, -2])
+    # images under the threshold were recomputed by the fp32 path: they carry fp32-grade numbers
+    s = np.sort(gl, 1)
+    redone = s[:, -1] - s[:, -2] < tau * 0.5
+    assert redone.any()
+    assert np.abs(gl[redone] - lg[redone]).max() <= 1e-4
+    assert np.abs(gp[redone] - pr[redone]).max() <= 1e-5
+    tl, tp = TOL[prec]
+    assert np.abs(gl - lg).max() <= tl and np.abs(gp - pr).max() <= tp
+
+
+@pytest.mark.parametrize("n", [1, 7, 8, 9, 15, 16, 17, 33, 2369])
+def test_tc_batch_edges(sib, oracle, presets, n):
+    m = presets["cifar-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 64, n)
+    lg, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=4096) as e:
+        gp, gl, ga = e.forward_sync(x)
+    assert gp.shape == (n, 10)
+    assert np.abs(gl - lg).max() <= 5e-2 and np.abs(gp - pr).max() <= 1e-2
+
+
+def test_tc_full_size_properties(sib, presets):
+    m = presets["cifar-lenet5"]
+    n = 16384
+    x = sib.modelspec.synthetic_images(m, 65, n)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=n, guard=False) as e:
+        p1, l1, a1 = e.forward_sync(x)
+        p2, l2, a2 = e.forward_sync(x)
+        assert l1.tobytes() == l2.tobytes() and p1.tobytes() == p2.tobytes()     # deterministic
+        perm = np.random.default_rng(1).permutation(n)
+        p3, l3, a3 = e.forward_sync(x[perm])
+        assert l3.tobytes() == l1[perm].tobytes()                                   # position in the tile is irrelevant
+        np.testing.assert_allclose(p1.sum(1), 1.0, atol=1e-5)
+        assert np.isfinite(l1).all()
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=n, guard=True) as e:
+        p4, l4, a4 = e.forward_sync(x)
+        p5, l5, a5 = e.forward_sync(x)
+        assert l4.tobytes() == l5.tobytes()        # the guard list's order is arbitrary, its effect is not
+        st = e.stats()
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=n) as e:
+        pf, lf, af = e.forward_sync(x)
+    assert (a4 == af).all()                        # guarded tensor path == fp32 path, image by image
+    assert np.abs(l4 - lf).max() <= 5e-2
+
+
+def test_engine_micro_batches_on_tc_path(sib, oracle, presets):
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 66, 200)
+    _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), max_batch=48, deadline_us=500) as e:   # default precision (FP16), guard on
+        got = []
+        for i in range(200):
+            while e.submit_f32(i, x[i]) == sib.native.EAGAIN:
+                got += e.poll(timeout_us=1000)
+        e.flush()
+        while len(got) < 200:
+            got += e.poll(timeout_us=100000)
+        assert [t for t, *_ in got] == list(range(200))
+        P = np.concatenate([p for _, p, _, _ in got])
+        assert np.abs(P - pr).max() <= 1e-2
+        assert (np.concatenate([a for _, _, a, _ in got]) == pr.argmax(1)).all()
