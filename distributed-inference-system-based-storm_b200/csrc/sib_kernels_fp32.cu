@@ -15,7 +15,10 @@ namespace sib {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kImgs = 4;  // images per CTA: dense-layer weights are read once per CTA and reused across them
+// Images per CTA. 4 for whole batches: dense-layer weights are read once per CTA and reused across the images.
+// 1 for the margin guard's short list (a few hundred images): there the latency of one CTA is what counts, so
+// each image gets a CTA of its own and the conv stages are cut into finer work items (CO_T below).
+constexpr int kImgsBatch = 4;
 
 template <int CO_T>
 __device__ __forceinline__ void conv_relu_pool(const float* __restrict__ in, int in_stride, float* __restrict__ out,
@@ -69,6 +72,7 @@ __device__ __forceinline__ void conv_relu_pool(const float* __restrict__ in, int
     }
 }
 
+template <int kImgs>
 __device__ __forceinline__ void dense_layer(const float* __restrict__ in, int in_stride, float* __restrict__ out,
                                             int out_stride, int K, int M, const float* __restrict__ wt,
                                             const float* __restrict__ bias, bool relu, int imgs) {
@@ -106,6 +110,7 @@ __device__ __forceinline__ void dense_layer(const float* __restrict__ in, int in
     (void)total;
 }
 
+template <int kImgs>
 __global__ void __launch_bounds__(kThreads) forward_fp32_kernel(DeviceModel m, const float* __restrict__ in, int n,
                                                                const int32_t* __restrict__ idx,
                                                                const int32_t* __restrict__ count,
@@ -144,14 +149,17 @@ __global__ void __launch_bounds__(kThreads) forward_fp32_kernel(DeviceModel m, c
             const float* wt = m.weights + L.w_off;
             const float* bs = m.weights + L.b_off;
             if (L.kind == kKindConv) {
-                if (L.d <= 6) conv_relu_pool<6>(cur, stride, nxt, stride, H, W, Cc, L.a, L.b, L.d, wt, bs, kImgs);
+                // output channels per work item: wide for batches (register reuse), narrow for the 1-image guard CTA
+                if (kImgs == 1 && L.d > 6) conv_relu_pool<2>(cur, stride, nxt, stride, H, W, Cc, L.a, L.b, L.d, wt, bs, kImgs);
+                else if (kImgs == 1) conv_relu_pool<3>(cur, stride, nxt, stride, H, W, Cc, L.a, L.b, L.d, wt, bs, kImgs);
+                else if (L.d <= 6) conv_relu_pool<6>(cur, stride, nxt, stride, H, W, Cc, L.a, L.b, L.d, wt, bs, kImgs);
                 else conv_relu_pool<8>(cur, stride, nxt, stride, H, W, Cc, L.a, L.b, L.d, wt, bs, kImgs);
                 H = (H - L.a + 1) >> 1;
                 W = (W - L.b + 1) >> 1;
                 Cc = L.d;
                 __syncthreads();
             } else {
-                dense_layer(cur, stride, nxt, stride, L.a, L.b, wt, bs, (L.flags & 1u) != 0, kImgs);
+                dense_layer<kImgs>(cur, stride, nxt, stride, L.a, L.b, wt, bs, (L.flags & 1u) != 0, kImgs);
             }
             float* t = cur; cur = nxt; nxt = t;
         }
@@ -191,27 +199,37 @@ __global__ void __launch_bounds__(kThreads) forward_fp32_kernel(DeviceModel m, c
 
 }  // namespace
 
-int fp32_smem_bytes(const DeviceModel& m) { return (int)(2u * kImgs * m.max_store_act * sizeof(float)); }
+int fp32_smem_bytes(const DeviceModel& m) { return (int)(2u * kImgsBatch * m.max_store_act * sizeof(float)); }
 
-int launch_forward_fp32(const DeviceModel& m, const float* d_in, int n, const int32_t* d_idx, const int32_t* d_count,
-                        float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin, void* stream) {
-    if (n <= 0) return 0;
+template <int kImgs>
+static int launch_inst(const DeviceModel& m, const float* d_in, int n, int expected, const int32_t* d_idx,
+                       const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin,
+                       cudaStream_t st) {
     static int configured_for[64] = {};
-    int smem = fp32_smem_bytes(m);
+    const int smem = (int)(2u * kImgs * m.max_store_act * sizeof(float));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     if (configured_for[dev & 63] < smem) {  // function attributes are per device
-        cudaError_t e = cudaFuncSetAttribute(forward_fp32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(forward_fp32_kernel<kImgs>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return (int)e;
         configured_for[dev & 63] = smem;
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int ctas = (n + kImgs - 1) / kImgs;
-    int per_sm = smem > 0 ? max(1, min(8, (227 * 1024) / (smem + 1024))) : 8;
-    int grid = min(ctas, sms * per_sm);
-    forward_fp32_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(m, d_in, n, d_idx, d_count, d_probs, d_logits,
-                                                                        d_argmax, d_margin);
+    const int ctas = (expected + kImgs - 1) / kImgs;  // the kernel grid-strides, so fewer CTAs than items is fine
+    const int per_sm = max(1, min(8, (227 * 1024) / (smem + 1024)));
+    const int grid = min(ctas, sms * per_sm);
+    forward_fp32_kernel<kImgs><<<grid, kThreads, smem, st>>>(m, d_in, n, d_idx, d_count, d_probs, d_logits, d_argmax, d_margin);
     return (int)cudaGetLastError();
+}
+
+int launch_forward_fp32(const DeviceModel& m, const float* d_in, int n, const int32_t* d_idx, const int32_t* d_count,
+                        float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin, void* stream) {
+    if (n <= 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    // d_idx != null is the margin guard: a short list whose length is only known on the device. Size the grid for
+    // a generous share of the batch (the list is ~2% of it); CTAs past the real count exit at once.
+    if (d_idx) return launch_inst<1>(m, d_in, n, min(n, max(1024, n / 8)), d_idx, d_count, d_probs, d_logits, d_argmax, d_margin, st);
+    return launch_inst<kImgsBatch>(m, d_in, n, n, d_idx, d_count, d_probs, d_logits, d_argmax, d_margin, st);
 }
 
 }  // namespace sib

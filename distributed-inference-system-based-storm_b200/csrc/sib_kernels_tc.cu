@@ -34,9 +34,12 @@
 namespace sib {
 namespace {
 
+// 12 warps = 3 per SM sub-partition, so each thread may hold 168 registers (the register file is split per
+// sub-partition: a 4th warp there would cap every thread at 128 and spill the sliding windows).
+// Sub-partition = warp % 4: each gets 2 conv1 warps + (a conv2 warp | the fc warp): 245*2+333 vs 245*2+256 mma / 8 images.
 constexpr int kConv1Warps = 8;
-constexpr int kConv2Warps = 4;
-constexpr int kFcWarps = 4;
+constexpr int kConv2Warps = 3;
+constexpr int kFcWarps = 1;
 constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps;
 constexpr int kThreadsTc = kWarps * 32;
 constexpr int kG = 8;     // images per ring slot (conv stages)
@@ -53,15 +56,21 @@ struct Net {
     static constexpr int K1ROW = 5 * C;             // real K per kernel row of conv1 (<= 15)
     static constexpr int SPANS = kG * OW1 / 32;     // conv1 work items per slot: 32 output columns x all rows
     static constexpr int TILES2 = kG * OW2 / 16;    // conv2 M tiles per slot
-    static constexpr int ITEMS2 = TILES2 * 2;       // x 2 N tiles
     static constexpr int FEAT = PH2 * PW2 * C2;     // 400 | 256
     static constexpr int KS1 = FEAT / 16;
-    static constexpr int P1_ROW = PW1 * C1, P1_IMG = PH1 * P1_ROW;  // halves
+    static constexpr int P1_ROW = PW1 * C1;                         // halves
+    // image stride of the pooled conv1 map, padded so that a conv2 tile that straddles two images keeps hitting
+    // distinct banks: stride/2 = 3*OW2 (mod 32) continues the 3-words-per-column progression across the seam
+    static constexpr int P1_IMG = PH1 * P1_ROW + (((3 * OW2 - PH1 * P1_ROW / 2) % 32 + 32) % 32) * 2;
     static constexpr int P1_BUF = kG * P1_IMG + 16;                 // + slack for the K-padding over-read
+    static constexpr int NB1 = 3;                                   // p1 ring slots
     static constexpr int P2_STRIDE = FEAT + 8;                      // halves; +8 keeps A-fragment loads conflict-free
     static constexpr int P2_BUF = kPair * P2_STRIDE;
     static constexpr int H1_STRIDE = 136, H2_STRIDE = 104;
-    static constexpr int PD = (H % 8 == 0) ? 8 : 7;                 // rows in flight per conv1 warp
+    // Input staging. H % 8 == 0: two register batches of 4 rows (2 scoreboard slots, no shared-memory cost).
+    // Otherwise: a cp.async ring of PD rows per warp (in-order groups, costs ~10 shared-memory wavefronts a row).
+    static constexpr bool REG_STAGE = (H % 8 == 0);
+    static constexpr int PD = REG_STAGE ? 8 : 7;                    // rows in flight per conv1 warp
     static constexpr int NCHUNK = (40 * C + 3) / 4;                 // 16-byte chunks per staged span row
     static constexpr int RING_ROW = ((40 * C + 16 + 7) / 8) * 8;    // halves per staged row incl. zero slack
     static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && H % PD == 0, "tiling");
@@ -69,8 +78,9 @@ struct Net {
     // packed weight image (32-bit words)
     static constexpr int W_C1 = 0;                               // [2 variants][5 kh][32 lanes][2]
     static constexpr int W_C2 = W_C1 + 2 * 5 * 64;               // [5 kh][2 ks][2 nt][32][2]
-    static constexpr int W_F1 = W_C2 + 5 * 2 * 2 * 64;           // [KS1][16 nt][32][2]
-    static constexpr int W_F2 = W_F1 + KS1 * 16 * 64;            // [8 ks][12 nt][32][2]
+    static constexpr int NT1 = 15;                               // fc1 N tiles: 120 outputs, no padding tile
+    static constexpr int W_F1 = W_C2 + 5 * 2 * 2 * 64;           // [KS1][NT1][32][2]
+    static constexpr int W_F2 = W_F1 + KS1 * NT1 * 64;           // [8 ks][12 nt][32][2]
     static constexpr int W_F3 = W_F2 + 8 * 12 * 64;              // [6 ks][2 nt][32][2]
     static constexpr int W_BIAS = W_F3 + 6 * 2 * 64;             // fp32: c1[8] c2[16] f1[128] f2[96] f3[16]
     static constexpr int W_TOTAL = W_BIAS + 8 + 16 + 128 + 96 + 16;
@@ -79,13 +89,16 @@ struct Net {
     static constexpr int S_FCW_BYTES = (W_BIAS - W_F1) * 4;
     static constexpr int S_BIAS = S_FCW + S_FCW_BYTES;                     // 264 floats
     static constexpr int S_P1 = S_BIAS + 264 * 4;
-    static constexpr int S_P2 = S_P1 + 2 * P1_BUF * 2;
+    static constexpr int S_P2 = S_P1 + NB1 * P1_BUF * 2;
     static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
     static constexpr int S_H2 = S_H1 + kPair * H1_STRIDE * 2;
     static constexpr int S_RING = S_H2 + kPair * H2_STRIDE * 2;
-    static constexpr int S_BAR = S_RING + kConv1Warps * 2 * RING_ROW * 2;
-    static constexpr int S_TOTAL = S_BAR + 8 * 8;
-    static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_BAR % 8 == 0, "align");
+    static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
+    static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * RING_ROW * 2; // cp.async landing zone: PD rows per conv1 warp
+    static constexpr int S_BAR = S_STAGE + (REG_STAGE ? 0 : kConv1Warps * PD * STAGE_ROW);
+    static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2, N_BAR = 2 * NB1 + 4;
+    static constexpr int S_TOTAL = S_BAR + N_BAR * 8;
+    static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_STAGE % 16 == 0 && S_BAR % 8 == 0, "align");
     static_assert(S_TOTAL <= 227 * 1024, "shared memory");
 };
 
@@ -115,7 +128,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         }
     }
 }
-__device__ __forceinline__ void fc_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kFcWarps * 32) : "memory"); }
 
 template <typename T> struct Ops;
 template <> struct Ops<__half> {
@@ -144,6 +156,21 @@ template <> struct Ops<__nv_bfloat16> {
 };
 
 __device__ __forceinline__ uint32_t lds32(const uint16_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+// cp.async (LDGSTS): global -> shared without a register stop-over. Its commit/wait groups complete in order, so a
+// deep prefetch queue costs no scoreboard slots (8 individually tracked LDGs do not fit the 6 slots a warp has:
+// profiles/ncu_tc_r01_notes.md shows the register-prefetch version paying one full memory latency per row).
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ float4 ldg_stream(const float* p) {
     float4 v;
     asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
@@ -166,13 +193,13 @@ struct TcParams {
 
 // ---- conv1 role ---------------------------------------------------------------------------------------------
 
-template <typename N, typename T>
+template <typename N, typename T, bool DBG>
 __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* smem, int cw, int lane) {
     const int g = lane >> 2, t = lane & 3;
     uint16_t* ring = reinterpret_cast<uint16_t*>(smem + N::S_RING) + cw * 2 * N::RING_ROW;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-    uint64_t* p1_full = bars + 0;   // [2]
-    uint64_t* p1_empty = bars + 2;  // [2]
+    uint64_t* p1_full = bars + N::B_P1F;   // [NB1]
+    uint64_t* p1_empty = bars + N::B_P1E;  // [NB1]
     // B fragments of conv1: even-column tiles and odd-column tiles (K shifted by one element so that odd columns
     // read 4-byte aligned pairs from the staged row)
     uint32_t bE[5][2], bO[5][2];
@@ -193,30 +220,42 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         valid = pair < nPairs;
         img0 = pair * kPair + (lq & 1) * kG;
     };
-    // per-lane source of the 16-byte chunk this lane stages for span s of a slot
+    // Every lane copies one 16-byte chunk of the span row; lanes past the last chunk repeat it (same bytes to the
+    // same address), which keeps the whole staging path free of divergent branches.
+    const int chunk = lane < N::NCHUNK ? lane : N::NCHUNK - 1;
     auto chunk_ptr = [&](int img0, int s) -> const float* {
         const int p0 = 32 * s;
         const int u_start = (p0 / N::OW1) * N::W + p0 % N::OW1;
-        const int F0 = u_start * N::C + 4 * lane;
+        const int F0 = u_start * N::C + 4 * chunk;
         int img = img0 + F0 / N::ROWF;
         img = min(img, P.n - 1);  // tail slots re-read the last image; their outputs are never written
         return P.in + (size_t)img * N::IMG + F0 % N::ROWF;
     };
 
-    float4 pre[N::PD];
+    const uint32_t stage = smem_u32(smem + N::S_STAGE) + cw * N::PD * N::STAGE_ROW + chunk * 16;
     int gs = cw;
     int img0;
     bool valid;
     span_src(gs, img0, valid);
     if (!valid) return;
     const float* src = chunk_ptr(img0, gs % N::SPANS);
+    float4 preA[4], preB[4];  // REG_STAGE: rows 8k..8k+3 / 8k+4..8k+7 of the span, one 16-byte chunk per lane
+    if constexpr (N::REG_STAGE) {
 #pragma unroll
-    for (int r = 0; r < N::PD; r++)
-        if (lane < N::NCHUNK) pre[r] = ldg_stream(src + r * N::ROWF);
+        for (int r = 0; r < 4; r++) preA[r] = ldg_stream(src + r * N::ROWF);
+#pragma unroll
+        for (int r = 0; r < 4; r++) preB[r] = ldg_stream(src + (4 + r) * N::ROWF);
+    } else {
+#pragma unroll
+        for (int r = 0; r < N::PD; r++) {
+            cp_async16(stage + r * N::STAGE_ROW, src + r * N::ROWF);
+            cp_async_commit();
+        }
+    }
 
     while (valid) {
         const int s = gs % N::SPANS, lq = gs / N::SPANS;
-        const int buf = lq & 1, use = lq >> 1;
+        const int buf = lq % N::NB1, use = lq / N::NB1;
         uint16_t* p1 = reinterpret_cast<uint16_t*>(smem + N::S_P1) + buf * N::P1_BUF;
         // next span (for the tail prefetch)
         int n_img0;
@@ -229,47 +268,80 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         const int u_start = (p0 / N::OW1) * N::W + p0 % N::OW1;
         auto uoff = [&](int p) { return ((p / N::OW1) * N::W + p % N::OW1 - u_start) * N::C; };
         const int offE0 = uoff(p0 + 2 * g) + 2 * t, offE1 = uoff(p0 + 2 * g + 16) + 2 * t;
-        const int offO0 = uoff(p0 + 2 * g + 1) - 1 + 2 * t, offO1 = uoff(p0 + 2 * g + 17) - 1 + 2 * t;
+        // odd columns sit C elements further in the same image row and read one element earlier: a constant C-1
+        constexpr int kOdd = N::C - 1;
         // pooled output columns of this lane
         const int pp0 = 16 * s + g, pp1 = pp0 + 8;
         const int o0 = (pp0 / N::PW1) * N::P1_IMG + (pp0 % N::PW1) * N::C1 + 2 * t;
         const int o1 = (pp1 / N::PW1) * N::P1_IMG + (pp1 % N::PW1) * N::C1 + 2 * t;
-        const bool dump = P.dbg && blockIdx.x == 0 && lq < 2;
-
-        mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
+        const bool dump = DBG && P.dbg && blockIdx.x == 0 && lq < 2;
 
         uint32_t aE[5][4], aO[5][4];
         float prev[4];
+        // stage(r): row r's cp.async group has landed -> fp32 to half into ring[r&1]; refill the landing slot
+        auto stage_row = [&](int r) {
+            float4 v;
+            if constexpr (N::REG_STAGE) {
+                v = ((r >> 2) & 1) ? preB[r & 3] : preA[r & 3];
+            } else {
+                cp_async_wait<N::PD - 1>();
+                v = lds128(stage + (r % N::PD) * N::STAGE_ROW);  // bytes this lane copied itself
+            }
+            uint2 pk;
+            pk.x = Ops<T>::pack(v.x, v.y);
+            pk.y = Ops<T>::pack(v.z, v.w);
+            *reinterpret_cast<uint2*>(ring + (r & 1) * N::RING_ROW + 4 * chunk) = pk;
+            // refill: same span while rows remain, else the first rows of this warp's next span (n_src is a valid
+            // address even when there is no next span, so the loads need no branch)
+            auto row_ptr = [&](int row) { return row < N::H ? src + row * N::ROWF : n_src + (row - N::H) * N::ROWF; };
+            if constexpr (N::REG_STAGE) {
+                if ((r & 3) == 3) {  // batch drained: fetch the batch two ahead (rows r+5 .. r+8) in one burst
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float4 nv = ldg_stream(row_ptr(r + 5 + j));
+                        if ((r >> 2) & 1) preB[j] = nv; else preA[j] = nv;
+                    }
+                }
+            } else {
+                if (r + N::PD < N::H || n_valid) cp_async16(stage + (r % N::PD) * N::STAGE_ROW, row_ptr(r + N::PD));
+                cp_async_commit();  // one group per row, empty or not, keeps the wait depth constant
+            }
+            // and pull the row two windows ahead into L2 (one 128-byte line per 8 chunks)
+            if ((lane & 7) == 0 && (r + 2 * N::PD < N::H || n_valid)) prefetch_l2(row_ptr(r + 2 * N::PD));
+        };
+        // frags(r): im2col A fragments of staged row r for the even-column and the odd-column tile
+        auto load_frags = [&](int r) {
+            __syncwarp();
+            const uint16_t* rr = ring + (r & 1) * N::RING_ROW;
+            uint32_t(&e)[4] = aE[r % 5];
+            uint32_t(&o)[4] = aO[r % 5];
+            e[0] = lds32(rr + offE0); e[1] = lds32(rr + offE1); e[2] = lds32(rr + offE0 + 8); e[3] = lds32(rr + offE1 + 8);
+            o[0] = lds32(rr + offE0 + kOdd); o[1] = lds32(rr + offE1 + kOdd);
+            o[2] = lds32(rr + offE0 + kOdd + 8); o[3] = lds32(rr + offE1 + kOdd + 8);
+        };
+
+        stage_row(0);
+        mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
+        load_frags(0);
+        // Software pipeline: while the mma of output row h-4 run, row h+1 is staged and its fragments are fetched,
+        // so neither the shared-memory round trip nor the mma dependency chains sit on the critical path.
 #pragma unroll
         for (int h = 0; h < N::H; h++) {
-            // stage row h: fp32 -> half, 8 bytes per lane
-            uint16_t* rr = ring + (h & 1) * N::RING_ROW;
-            if (lane < N::NCHUNK) {
-                const float4 v = pre[h % N::PD];
-                uint2 pk;
-                pk.x = Ops<T>::pack(v.x, v.y);
-                pk.y = Ops<T>::pack(v.z, v.w);
-                *reinterpret_cast<uint2*>(rr + 4 * lane) = pk;
-                // refill the slot: same span while rows remain, else the first rows of this warp's next span
-                if (h + N::PD < N::H) pre[h % N::PD] = ldg_stream(src + (h + N::PD) * N::ROWF);
-                else if (n_valid) pre[h % N::PD] = ldg_stream(n_src + (h + N::PD - N::H) * N::ROWF);
-            }
-            __syncwarp();
-            {
-                uint32_t(&e)[4] = aE[h % 5];
-                uint32_t(&o)[4] = aO[h % 5];
-                e[0] = lds32(rr + offE0); e[1] = lds32(rr + offE1); e[2] = lds32(rr + offE0 + 8); e[3] = lds32(rr + offE1 + 8);
-                o[0] = lds32(rr + offO0); o[1] = lds32(rr + offO1); o[2] = lds32(rr + offO0 + 8); o[3] = lds32(rr + offO1 + 8);
-            }
+            if (h + 1 < N::H) stage_row(h + 1);
+            float cE[4] = {0.f, 0.f, 0.f, 0.f}, cO[4] = {0.f, 0.f, 0.f, 0.f};
+            float dE[4] = {0.f, 0.f, 0.f, 0.f}, dO[4] = {0.f, 0.f, 0.f, 0.f};
             if (h >= 4) {
                 const int oh = h - 4;
-                float cE[4] = {0.f, 0.f, 0.f, 0.f}, cO[4] = {0.f, 0.f, 0.f, 0.f};
-                float dE[4] = {0.f, 0.f, 0.f, 0.f}, dO[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                for (int kh = 0; kh < 5; kh++) {  // two accumulator chains per tile keep 4 mma in flight
-                    if (kh < 3) { Ops<T>::mma(cE, aE[(oh + kh) % 5], bE[kh]); Ops<T>::mma(cO, aO[(oh + kh) % 5], bO[kh]); }
-                    else        { Ops<T>::mma(dE, aE[(oh + kh) % 5], bE[kh]); Ops<T>::mma(dO, aO[(oh + kh) % 5], bO[kh]); }
-                }
+                // kernel row 0 first: it reads the window slot that row h+1 is about to overwrite
+                Ops<T>::mma(cE, aE[(oh + 0) % 5], bE[0]); Ops<T>::mma(cO, aO[(oh + 0) % 5], bO[0]);
+                Ops<T>::mma(dE, aE[(oh + 3) % 5], bE[3]); Ops<T>::mma(dO, aO[(oh + 3) % 5], bO[3]);
+                Ops<T>::mma(cE, aE[(oh + 1) % 5], bE[1]); Ops<T>::mma(cO, aO[(oh + 1) % 5], bO[1]);
+                Ops<T>::mma(dE, aE[(oh + 4) % 5], bE[4]); Ops<T>::mma(dO, aO[(oh + 4) % 5], bO[4]);
+                Ops<T>::mma(cE, aE[(oh + 2) % 5], bE[2]); Ops<T>::mma(cO, aO[(oh + 2) % 5], bO[2]);
+            }
+            if (h + 1 < N::H) load_frags(h + 1);
+            if (h >= 4) {
+                const int oh = h - 4;
                 float m[4];
 #pragma unroll
                 for (int i = 0; i < 4; i++) m[i] = fmaxf(cE[i] + dE[i], cO[i] + dO[i]);  // pool over the column pair
@@ -284,10 +356,11 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
                     if (t < 3) {
                         *reinterpret_cast<uint32_t*>(p1 + o0 + ph * N::P1_ROW) = Ops<T>::pack(v0, v1);
                         *reinterpret_cast<uint32_t*>(p1 + o1 + ph * N::P1_ROW) = Ops<T>::pack(v2, v3);
-                        if (dump) {
-                            float* d = P.dbg + lq * kG * N::P1_IMG;
-                            d[o0 + ph * N::P1_ROW] = v0; d[o0 + ph * N::P1_ROW + 1] = v1;
-                            d[o1 + ph * N::P1_ROW] = v2; d[o1 + ph * N::P1_ROW + 1] = v3;
+                        if (dump) {  // dense [img][ph][pw][c] for the test, not the padded ring layout
+                            float* d = P.dbg + lq * kG * N::PH1 * N::P1_ROW + ph * N::P1_ROW + 2 * t;
+                            const int d0 = (pp0 / N::PW1) * N::PH1 * N::P1_ROW + (pp0 % N::PW1) * N::C1;
+                            const int d1 = (pp1 / N::PW1) * N::PH1 * N::P1_ROW + (pp1 % N::PW1) * N::C1;
+                            d[d0] = v0; d[d0 + 1] = v1; d[d1] = v2; d[d1 + 1] = v3;
                         }
                     }
                 }
@@ -303,34 +376,33 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
 
 // ---- conv2 role ---------------------------------------------------------------------------------------------
 
-template <typename N, typename T>
+template <typename N, typename T, bool DBG>
 __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* smem, int w2, int lane) {
     const int g = lane >> 2, t = lane & 3;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-    uint64_t* p1_full = bars + 0;
-    uint64_t* p1_empty = bars + 2;
-    uint64_t* p2_full = bars + 4;
-    uint64_t* p2_empty = bars + 6;
-    const int nt = w2 & 1;  // items of one warp always share the N tile: item = tile*2 + nt, ITEMS2 is even
-    static_assert(N::ITEMS2 % 2 == 0 && kConv2Warps % 2 == 0, "nt must be constant per warp");
-    uint32_t bW[5][2][2];
+    uint64_t* p1_full = bars + N::B_P1F;
+    uint64_t* p1_empty = bars + N::B_P1E;
+    uint64_t* p2_full = bars + N::B_P2F;
+    uint64_t* p2_empty = bars + N::B_P2E;
+    uint32_t bW[5][2][2][2];  // [kh][k step][n tile][reg]: the whole 150x16 filter, register-resident
 #pragma unroll
     for (int kh = 0; kh < 5; kh++)
 #pragma unroll
-        for (int ks = 0; ks < 2; ks++) {
-            const uint2 v = *reinterpret_cast<const uint2*>(P.wpack + N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64 + lane * 2);
-            bW[kh][ks][0] = v.x; bW[kh][ks][1] = v.y;
-        }
+        for (int ks = 0; ks < 2; ks++)
+#pragma unroll
+            for (int nt = 0; nt < 2; nt++) {
+                const uint2 v = *reinterpret_cast<const uint2*>(P.wpack + N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64 + lane * 2);
+                bW[kh][ks][nt][0] = v.x; bW[kh][ks][nt][1] = v.y;
+            }
     const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS) + 8;
-    const float bias0 = biasp[nt * 8 + 2 * t], bias1 = biasp[nt * 8 + 2 * t + 1];
+    const float bias00 = biasp[2 * t], bias01 = biasp[2 * t + 1], bias10 = biasp[8 + 2 * t], bias11 = biasp[8 + 2 * t + 1];
     const int nPairs = (P.n + kPair - 1) / kPair;
 
-    for (int gi = w2;; gi += kConv2Warps) {
-        const int lq = gi / N::ITEMS2, item = gi % N::ITEMS2;
+    for (int gi = w2;; gi += kConv2Warps) {  // M tiles in CTA order, dealt round-robin to the conv2 warps
+        const int lq = gi / N::TILES2, tile = gi % N::TILES2;
         const int Qi = lq >> 1;
         if ((int)(blockIdx.x + Qi * gridDim.x) >= nPairs) break;
-        const int tile = item >> 1;
-        const int buf1 = lq & 1, use1 = lq >> 1;
+        const int buf1 = lq % N::NB1, use1 = lq / N::NB1;
         const int buf2 = Qi & 1, use2 = Qi >> 1;
         const uint16_t* p1 = reinterpret_cast<const uint16_t*>(smem + N::S_P1) + buf1 * N::P1_BUF;
         uint16_t* p2 = reinterpret_cast<uint16_t*>(smem + N::S_P2) + buf2 * N::P2_BUF;
@@ -339,17 +411,15 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
         const int imgl = Pe / N::OW2, ow = Pe % N::OW2;
         const int offA0 = imgl * N::P1_IMG + ow * N::C1 + 2 * t;  // even column (rows g)
         const int offA1 = offA0 + N::C1;                           // odd column  (rows g+8)
-        const int pw = ow >> 1;
-        const int o2 = ((lq & 1) * kG + imgl) * N::P2_STRIDE + pw * N::C2 + nt * 8 + 2 * t;
-        const bool dump = P.dbg && blockIdx.x == 0 && Qi == 0;
+        const int o2 = ((lq & 1) * kG + imgl) * N::P2_STRIDE + (ow >> 1) * N::C2 + 2 * t;
+        const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
 
         mbar_wait(&p1_full[buf1], use1 & 1);
         mbar_wait(&p2_empty[buf2], (use2 & 1) ^ 1);
 
         uint32_t a[5][2][4];
-        float prev0 = 0.f, prev1 = 0.f;
-#pragma unroll
-        for (int r = 0; r < N::PH1; r++) {
+        float prev[4] = {0.f, 0.f, 0.f, 0.f};
+        auto load_frags = [&](int r) {
             const uint16_t* row = p1 + r * N::P1_ROW;
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {
@@ -359,25 +429,39 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
                 f[2] = lds32(row + offA0 + ks * 16 + 8);
                 f[3] = lds32(row + offA1 + ks * 16 + 8);
             }
-            if (r >= 4) {
-                const int oh = r - 4;
-                float c[4] = {0.f, 0.f, 0.f, 0.f}, d[4] = {0.f, 0.f, 0.f, 0.f};
+        };
 #pragma unroll
-                for (int kh = 0; kh < 5; kh++) {
-                    Ops<T>::mma(c, a[(oh + kh) % 5][0], bW[kh][0]);
-                    Ops<T>::mma(d, a[(oh + kh) % 5][1], bW[kh][1]);
-                }
-                const float h0 = fmaxf(c[0] + d[0], c[2] + d[2]), h1 = fmaxf(c[1] + d[1], c[3] + d[3]);
-                if ((oh & 1) == 0) {
-                    prev0 = h0; prev1 = h1;
-                } else {
-                    const int ph = oh >> 1;
-                    const float v0 = fmaxf(fmaxf(h0, prev0) + bias0, 0.f), v1 = fmaxf(fmaxf(h1, prev1) + bias1, 0.f);
-                    *reinterpret_cast<uint32_t*>(p2 + o2 + ph * N::PW2 * N::C2) = Ops<T>::pack(v0, v1);
-                    if (dump) {
-                        float* dd = P.dbg + 2 * kG * N::P1_IMG;
-                        dd[o2 + ph * N::PW2 * N::C2] = v0; dd[o2 + ph * N::PW2 * N::C2 + 1] = v1;
-                    }
+        for (int r = 0; r < 4; r++) load_frags(r);
+#pragma unroll
+        for (int r = 4; r < N::PH1; r++) {
+            load_frags(r);  // consumed by the kh=4 mma at the end of this iteration's chains
+            const int oh = r - 4;
+            // 4 independent accumulator chains: (n tile) x (k step)
+            float c0[4] = {0.f, 0.f, 0.f, 0.f}, d0[4] = {0.f, 0.f, 0.f, 0.f};
+            float c1[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int kh = 0; kh < 5; kh++) {
+                Ops<T>::mma(c0, a[(oh + kh) % 5][0], bW[kh][0][0]);
+                Ops<T>::mma(c1, a[(oh + kh) % 5][0], bW[kh][0][1]);
+                Ops<T>::mma(d0, a[(oh + kh) % 5][1], bW[kh][1][0]);
+                Ops<T>::mma(d1, a[(oh + kh) % 5][1], bW[kh][1][1]);
+            }
+            // pool over the column pair (rows g / g+8 of the tile)
+            const float h[4] = {fmaxf(c0[0] + d0[0], c0[2] + d0[2]), fmaxf(c0[1] + d0[1], c0[3] + d0[3]),
+                                fmaxf(c1[0] + d1[0], c1[2] + d1[2]), fmaxf(c1[1] + d1[1], c1[3] + d1[3])};
+            if ((oh & 1) == 0) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) prev[i] = h[i];
+            } else {
+                const int ph = oh >> 1;
+                const float v0 = fmaxf(fmaxf(h[0], prev[0]) + bias00, 0.f), v1 = fmaxf(fmaxf(h[1], prev[1]) + bias01, 0.f);
+                const float v2 = fmaxf(fmaxf(h[2], prev[2]) + bias10, 0.f), v3 = fmaxf(fmaxf(h[3], prev[3]) + bias11, 0.f);
+                uint16_t* dst = p2 + o2 + ph * N::PW2 * N::C2;
+                *reinterpret_cast<uint32_t*>(dst) = Ops<T>::pack(v0, v1);      // channels 2t, 2t+1
+                *reinterpret_cast<uint32_t*>(dst + 8) = Ops<T>::pack(v2, v3);  // channels 8+2t, 9+2t
+                if (dump) {
+                    float* dd = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + o2 + ph * N::PW2 * N::C2;
+                    dd[0] = v0; dd[1] = v1; dd[8] = v2; dd[9] = v3;
                 }
             }
         }
@@ -386,14 +470,14 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
     }
 }
 
-// ---- fc role ------------------------------------------------------------------------------------------------
+// ---- fc role (one warp) -------------------------------------------------------------------------------------
 
-template <typename N, typename T>
-__device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, int fw, int lane) {
+template <typename N, typename T, bool DBG>
+__device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, int lane) {
     const int g = lane >> 2, t = lane & 3;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-    uint64_t* p2_full = bars + 4;
-    uint64_t* p2_empty = bars + 6;
+    uint64_t* p2_full = bars + N::B_P2F;
+    uint64_t* p2_empty = bars + N::B_P2E;
     const uint32_t* w1 = reinterpret_cast<const uint32_t*>(smem + N::S_FCW);
     const uint32_t* w2 = w1 + (N::W_F2 - N::W_F1);
     const uint32_t* w3 = w1 + (N::W_F3 - N::W_F1);
@@ -407,63 +491,64 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
         if (pair >= nPairs) break;
         const int buf = Qi & 1, use = Qi >> 1;
         const uint16_t* p2 = reinterpret_cast<const uint16_t*>(smem + N::S_P2) + buf * N::P2_BUF;
-        const bool dump = P.dbg && blockIdx.x == 0 && Qi == 0;
+        const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
         mbar_wait(&p2_full[buf], use & 1);
-        // ---- fc1: [16 x FEAT] . [FEAT x 128], 4 N tiles per warp
+        // ---- fc1: [16 x FEAT] . [FEAT x 120]: 15 N tiles = 15 independent accumulator chains
+        // (h1 columns 120..127 stay zero from the set-up; fc2's K padding multiplies them by zero weights)
         {
-            float acc[4][4];
+            float acc[N::NT1][4];
 #pragma unroll
-            for (int j = 0; j < 4; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            for (int j = 0; j < N::NT1; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
             const uint16_t* a0p = p2 + g * N::P2_STRIDE + 2 * t;
             const uint16_t* a1p = a0p + 8 * N::P2_STRIDE;
-#pragma unroll 5
+#pragma unroll 1
             for (int ks = 0; ks < N::KS1; ks++) {
                 uint32_t a[4];
                 a[0] = lds32(a0p + ks * 16); a[1] = lds32(a1p + ks * 16); a[2] = lds32(a0p + ks * 16 + 8); a[3] = lds32(a1p + ks * 16 + 8);
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const uint2 bv = *reinterpret_cast<const uint2*>(w1 + (ks * 16 + fw * 4 + j) * 64 + lane * 2);
+                for (int j = 0; j < N::NT1; j++) {
+                    const uint2 bv = *reinterpret_cast<const uint2*>(w1 + (ks * N::NT1 + j) * 64 + lane * 2);
                     const uint32_t b[2] = {bv.x, bv.y};
                     Ops<T>::mma(acc[j], a, b);
                 }
             }
             mbar_arrive(&p2_empty[buf]);  // p2 fully consumed by this lane
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int n0 = (fw * 4 + j) * 8 + 2 * t;
+            for (int j = 0; j < N::NT1; j++) {
+                const int n0 = j * 8 + 2 * t;
                 const float b0 = bias[24 + n0], b1 = bias[24 + n0 + 1];
                 const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
                 const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
                 *reinterpret_cast<uint32_t*>(h1 + g * N::H1_STRIDE + n0) = Ops<T>::pack(v0, v1);
                 *reinterpret_cast<uint32_t*>(h1 + (g + 8) * N::H1_STRIDE + n0) = Ops<T>::pack(v2, v3);
                 if (dump) {
-                    float* d = P.dbg + 2 * kG * N::P1_IMG + N::P2_BUF;
+                    float* d = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + N::P2_BUF;
                     d[g * 128 + n0] = v0; d[g * 128 + n0 + 1] = v1; d[(g + 8) * 128 + n0] = v2; d[(g + 8) * 128 + n0 + 1] = v3;
                 }
             }
         }
-        fc_bar();
-        // ---- fc2: [16 x 128] . [128 x 96], 3 N tiles per warp
+        __syncwarp();
+        // ---- fc2: [16 x 128] . [128 x 96]
         {
-            float acc[3][4];
+            float acc[12][4];
 #pragma unroll
-            for (int j = 0; j < 3; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            for (int j = 0; j < 12; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
             const uint16_t* a0p = h1 + g * N::H1_STRIDE + 2 * t;
             const uint16_t* a1p = a0p + 8 * N::H1_STRIDE;
-#pragma unroll
+#pragma unroll 1
             for (int ks = 0; ks < 8; ks++) {
                 uint32_t a[4];
                 a[0] = lds32(a0p + ks * 16); a[1] = lds32(a1p + ks * 16); a[2] = lds32(a0p + ks * 16 + 8); a[3] = lds32(a1p + ks * 16 + 8);
 #pragma unroll
-                for (int j = 0; j < 3; j++) {
-                    const uint2 bv = *reinterpret_cast<const uint2*>(w2 + (ks * 12 + fw * 3 + j) * 64 + lane * 2);
+                for (int j = 0; j < 12; j++) {
+                    const uint2 bv = *reinterpret_cast<const uint2*>(w2 + (ks * 12 + j) * 64 + lane * 2);
                     const uint32_t b[2] = {bv.x, bv.y};
                     Ops<T>::mma(acc[j], a, b);
                 }
             }
 #pragma unroll
-            for (int j = 0; j < 3; j++) {
-                const int n0 = (fw * 3 + j) * 8 + 2 * t;
+            for (int j = 0; j < 12; j++) {
+                const int n0 = j * 8 + 2 * t;
                 const float b0 = bias[152 + n0], b1 = bias[152 + n0 + 1];
                 const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
                 const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
@@ -471,9 +556,9 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
                 *reinterpret_cast<uint32_t*>(h2 + (g + 8) * N::H2_STRIDE + n0) = Ops<T>::pack(v2, v3);
             }
         }
-        fc_bar();
-        // ---- fc3 + softmax/argmax/margin: one warp; the others start the next pair's fc1 meanwhile
-        if (fw == 0) {
+        __syncwarp();
+        // ---- fc3 + softmax / argmax / top1-top2 margin
+        {
             float acc[2][4];
 #pragma unroll
             for (int j = 0; j < 2; j++) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
@@ -504,7 +589,7 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
                 int am = cls[0];
 #pragma unroll
                 for (int i = 1; i < 4; i++)
-                    if (x[i] > mx) { mx = x[i]; am = cls[i]; }  // ascending class order within the lane except 8,9
+                    if (x[i] > mx) { mx = x[i]; am = cls[i]; }
                 // quad reduction with first-maximum tie-break on the class index
 #pragma unroll
                 for (int o = 1; o <= 2; o <<= 1) {
@@ -515,7 +600,7 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
                 float second = -INFINITY;
 #pragma unroll
                 for (int i = 0; i < 4; i++)
-                    if (cls[i] != am || (i >= 2 && t != 0)) second = fmaxf(second, x[i]);
+                    if (cls[i] != am) second = fmaxf(second, x[i]);  // unused slots hold -inf
                 second = fmaxf(second, __shfl_xor_sync(0xffffffffu, second, 1));
                 second = fmaxf(second, __shfl_xor_sync(0xffffffffu, second, 2));
                 float e[4], s = 0.f;
@@ -541,10 +626,11 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
                 }
             }
         }
+        __syncwarp();  // h1/h2 are rewritten by the next pair
     }
 }
 
-template <typename N, typename T>
+template <typename N, typename T, bool DBG>
 __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -559,18 +645,20 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
         for (int i = threadIdx.x; i < (N::S_BAR - N::S_P1) / 4; i += blockDim.x) z[i] = 0u;  // p1,p2,h1,h2,rings
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+            for (int i = 0; i < N::NB1; i++) {
+                mbar_init(&bars[N::B_P1F + i], N::SPANS * 32);        // p1_full : every lane of every span
+                mbar_init(&bars[N::B_P1E + i], N::TILES2 * 32);       // p1_empty: every lane of every conv2 tile
+            }
             for (int i = 0; i < 2; i++) {
-                mbar_init(&bars[0 + i], N::SPANS * 32);               // p1_full : every lane of every span
-                mbar_init(&bars[2 + i], N::ITEMS2 * 32);              // p1_empty: every lane of every conv2 item
-                mbar_init(&bars[4 + i], 2 * N::ITEMS2 * 32);          // p2_full : two slots of conv2 items
-                mbar_init(&bars[6 + i], kFcWarps * 32);               // p2_empty: every fc lane
+                mbar_init(&bars[N::B_P2F + i], 2 * N::TILES2 * 32);   // p2_full : two slots of conv2 tiles
+                mbar_init(&bars[N::B_P2E + i], kFcWarps * 32);        // p2_empty: every fc lane
             }
         }
     }
     __syncthreads();
-    if (warp < kConv1Warps) conv1_role<N, T>(P, smem, warp, lane);
-    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T>(P, smem, warp - kConv1Warps, lane);
-    else fc_role<N, T>(P, smem, warp - kConv1Warps - kConv2Warps, lane);
+    if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
+    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
+    else fc_role<N, T, DBG>(P, smem, lane);
 }
 
 // ---- host side: weight packing ----------------------------------------------------------------------------------
@@ -620,7 +708,7 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
                     return (i < (int)D.a && j < (int)D.b) ? k[i * D.b + j] : 0.f;
                 });
     };
-    dense(N::W_F1, N::KS1, 16, L[2]);
+    dense(N::W_F1, N::KS1, N::NT1, L[2]);
     dense(N::W_F2, 8, 12, L[3]);
     dense(N::W_F3, 6, 2, L[4]);
     float* b = reinterpret_cast<float*>(&w[N::W_BIAS]);
@@ -632,21 +720,26 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
     return w;
 }
 
-template <typename N, typename T>
-int launch(const TcWeights& w, const TcParams& p, cudaStream_t st) {
+template <typename N, typename T, bool DBG>
+int launch_inst(const TcParams& p, cudaStream_t st) {
     static bool configured[64] = {};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {  // function attributes are per device
-        cudaError_t e = cudaFuncSetAttribute(forward_tc_kernel<N, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, N::S_TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(forward_tc_kernel<N, T, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, N::S_TOTAL);
         if (e != cudaSuccess) return (int)e;
         configured[dev & 63] = true;
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int pairs = (p.n + kPair - 1) / kPair;
     const int grid = pairs < sms ? pairs : sms;
-    forward_tc_kernel<N, T><<<grid, kThreadsTc, N::S_TOTAL, st>>>(p);
+    forward_tc_kernel<N, T, DBG><<<grid, kThreadsTc, N::S_TOTAL, st>>>(p);
     return (int)cudaGetLastError();
+}
+
+template <typename N, typename T>
+int launch(const TcWeights&, const TcParams& p, cudaStream_t st) {
+    return p.dbg ? launch_inst<N, T, true>(p, st) : launch_inst<N, T, false>(p, st);
 }
 
 using NetMnist = Net<28, 28, 1>;
@@ -679,8 +772,8 @@ void tc_release(TcWeights* w) {
 }
 
 size_t tc_debug_floats(int preset) {
-    return preset == 0 ? 2 * kG * NetMnist::P1_IMG + NetMnist::P2_BUF + 16 * 128
-                       : 2 * kG * NetCifar::P1_IMG + NetCifar::P2_BUF + 16 * 128;
+    return preset == 0 ? 2 * kG * NetMnist::PH1 * NetMnist::P1_ROW + NetMnist::P2_BUF + 16 * 128
+                       : 2 * kG * NetCifar::PH1 * NetCifar::P1_ROW + NetCifar::P2_BUF + 16 * 128;
 }
 
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
