@@ -159,7 +159,7 @@ int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_l
         e = launch_forward_tc(tc, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, nullptr, st);
         stats.kernel_launches += 1;
         if (!e && guard) {
-            e = launch_forward_fp32(dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, nullptr, st);
+            e = launch_guard_fp32(model.preset, dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, st);
             stats.kernel_launches += 1;
         }
     }

@@ -74,4 +74,8 @@ size_t tc_debug_floats(int preset);
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
                       GuardScratch* guard, float tau, float* d_dbg, void* stream);
 
+// fp32 recompute of the listed images, one image per CTA (sib_kernels_guard.cu). LeNet-5 presets only.
+int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const int32_t* d_list,
+                      const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, void* stream);
+
 }  // namespace sib

@@ -1,0 +1,241 @@
+// sib_kernels_guard.cu -- the margin guard's recompute path: fp32 CUDA-core LeNet-5 forward, one image per CTA.
+//
+// The tensor-core kernel lists the images whose top1-top2 logit margin is below tau (sib_kernels_tc.cu); this
+// kernel re-runs exactly those images in fp32 and overwrites their outputs, so that the emitted argmax equals the
+// fp32 path's (BASELINE.json: "argmax predictions must agree exactly"). The list is short (~2% of a batch), so what
+// matters is the latency of one image: a CTA owns an image, every stage is register-tiled so that FFMA, not
+// shared-memory traffic, is the limiter, and the dense weights are streamed from L2 with 128-bit loads.
+// Op semantics as in sib_kernels_fp32.cu (TF 1.x Conv2D/BiasAdd/Relu/MaxPool/MatMul/Softmax; InferenceBolt.java:81-85).
+#include <cuda_runtime.h>
+
+#include "sib_internal.hpp"
+
+namespace sib {
+namespace {
+
+constexpr int kGT = 256;
+
+template <int H_, int W_, int C_>
+struct GNet {
+    static constexpr int H = H_, W = W_, C = C_;
+    static constexpr int PH1 = (H - 4) / 2, PW1 = (W - 4) / 2, PH2 = (PH1 - 4) / 2, PW2 = (PW1 - 4) / 2;
+    static constexpr int C1 = 6, C2 = 16, F1 = 120, F2 = 84, F3 = 10;
+    static constexpr int IMG = H * W * C, P1 = PH1 * PW1 * C1, FEAT = PH2 * PW2 * C2;
+    static constexpr int NW1 = 25 * C * C1, NW2 = 25 * C1 * C2;
+    static constexpr int KSL = 8;  // k slices of fc1
+    static_assert(PH1 * PW1 <= kGT && PH2 * PW2 * 4 <= kGT && FEAT % KSL == 0 && IMG % 4 == 0, "mapping");
+    // shared memory (floats)
+    static constexpr int S_IMG = 0, S_W1 = S_IMG + IMG, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
+                         S_W2 = S_P1 + P1, S_P2 = S_W2 + NW2 + C2, S_PART = S_P2 + FEAT, S_H1 = S_PART + KSL * F1,
+                         S_H2 = S_H1 + F1, S_LG = S_H2 + 3 * F2, S_TOTAL = S_LG + 16;
+};
+
+template <typename G>
+__global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const float* __restrict__ in,
+                                                        const int32_t* __restrict__ list,
+                                                        const int32_t* __restrict__ count, int cap,
+                                                        float* __restrict__ probs, float* __restrict__ logits,
+                                                        int32_t* __restrict__ argmax) {
+    extern __shared__ __align__(16) float sm[];
+    const int tid = threadIdx.x;
+    const int n = min(*count, cap);
+    const float* W = m.weights;
+    const DeviceLayer L0 = m.layer[0], L1 = m.layer[1], L2 = m.layer[2], L3 = m.layer[3], L4 = m.layer[4];
+    // conv filters + biases stay in shared memory for every image this CTA handles
+    for (int i = tid; i < G::NW1; i += kGT) sm[G::S_W1 + i] = __ldg(W + L0.w_off + i);
+    for (int i = tid; i < G::C1; i += kGT) sm[G::S_W1 + G::NW1 + i] = __ldg(W + L0.b_off + i);
+    for (int i = tid; i < G::NW2; i += kGT) sm[G::S_W2 + i] = __ldg(W + L1.w_off + i);
+    for (int i = tid; i < G::C2; i += kGT) sm[G::S_W2 + G::NW2 + i] = __ldg(W + L1.b_off + i);
+
+    for (int it = blockIdx.x; it < n; it += gridDim.x) {
+        const int img = list[it];
+        __syncthreads();
+        {
+            const float4* s4 = reinterpret_cast<const float4*>(in + (size_t)img * G::IMG);
+            float4* d4 = reinterpret_cast<float4*>(sm + G::S_IMG);
+            for (int i = tid; i < G::IMG / 4; i += kGT) d4[i] = __ldg(s4 + i);
+        }
+        __syncthreads();
+        // ---- conv1 + bias + ReLU + pool: one thread per pooled position, 2x2 positions x 6 channels in registers
+        if (tid < G::PH1 * G::PW1) {
+            const int py = tid / G::PW1, px = tid % G::PW1;
+            float acc[2][2][G::C1];
+#pragma unroll
+            for (int a = 0; a < 2; a++)
+#pragma unroll
+                for (int b = 0; b < 2; b++)
+#pragma unroll
+                    for (int c = 0; c < G::C1; c++) acc[a][b][c] = 0.f;
+            const float* ip = sm + G::S_IMG + ((2 * py) * G::W + 2 * px) * G::C;
+#pragma unroll
+            for (int r = 0; r < 6; r++) {  // patch row r feeds output row dy with kernel row r-dy
+                float row[6 * G::C];
+#pragma unroll
+                for (int i = 0; i < 6 * G::C; i++) row[i] = ip[r * G::W * G::C + i];
+#pragma unroll
+                for (int dy = 0; dy < 2; dy++) {
+                    const int kh = r - dy;
+                    if (kh < 0 || kh > 4) continue;
+#pragma unroll
+                    for (int kw = 0; kw < 5; kw++)
+#pragma unroll
+                        for (int c = 0; c < G::C; c++) {
+                            const float* wp = sm + G::S_W1 + ((kh * 5 + kw) * G::C + c) * G::C1;  // broadcast reads
+#pragma unroll
+                            for (int co = 0; co < G::C1; co++) {
+                                const float w = wp[co];
+                                acc[dy][0][co] = fmaf(row[kw * G::C + c], w, acc[dy][0][co]);
+                                acc[dy][1][co] = fmaf(row[(kw + 1) * G::C + c], w, acc[dy][1][co]);
+                            }
+                        }
+                }
+            }
+#pragma unroll
+            for (int co = 0; co < G::C1; co++) {
+                const float mx = fmaxf(fmaxf(acc[0][0][co], acc[0][1][co]), fmaxf(acc[1][0][co], acc[1][1][co]));
+                sm[G::S_P1 + (py * G::PW1 + px) * G::C1 + co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + co], 0.f);
+            }
+        }
+        __syncthreads();
+        // ---- conv2 + bias + ReLU + pool: thread = (pooled position, 4 output channels)
+        if (tid < G::PH2 * G::PW2 * 4) {
+            const int q = tid & 3, pos = tid >> 2;
+            const int py = pos / G::PW2, px = pos % G::PW2;
+            float acc[2][2][4];
+#pragma unroll
+            for (int a = 0; a < 2; a++)
+#pragma unroll
+                for (int b = 0; b < 2; b++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++) acc[a][b][c] = 0.f;
+            const float* ip = sm + G::S_P1 + ((2 * py) * G::PW1 + 2 * px) * G::C1;
+#pragma unroll
+            for (int r = 0; r < 6; r++) {
+                float row[6 * G::C1];
+#pragma unroll
+                for (int i = 0; i < 6 * G::C1; i++) row[i] = ip[r * G::PW1 * G::C1 + i];
+#pragma unroll
+                for (int dy = 0; dy < 2; dy++) {
+                    const int kh = r - dy;
+                    if (kh < 0 || kh > 4) continue;
+#pragma unroll
+                    for (int kw = 0; kw < 5; kw++)
+#pragma unroll
+                        for (int c = 0; c < G::C1; c++) {
+                            const float4 w = *reinterpret_cast<const float4*>(sm + G::S_W2 + ((kh * 5 + kw) * G::C1 + c) * G::C2 + 4 * q);
+                            const float v0 = row[kw * G::C1 + c], v1 = row[(kw + 1) * G::C1 + c];
+                            acc[dy][0][0] = fmaf(v0, w.x, acc[dy][0][0]); acc[dy][0][1] = fmaf(v0, w.y, acc[dy][0][1]);
+                            acc[dy][0][2] = fmaf(v0, w.z, acc[dy][0][2]); acc[dy][0][3] = fmaf(v0, w.w, acc[dy][0][3]);
+                            acc[dy][1][0] = fmaf(v1, w.x, acc[dy][1][0]); acc[dy][1][1] = fmaf(v1, w.y, acc[dy][1][1]);
+                            acc[dy][1][2] = fmaf(v1, w.z, acc[dy][1][2]); acc[dy][1][3] = fmaf(v1, w.w, acc[dy][1][3]);
+                        }
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const float mx = fmaxf(fmaxf(acc[0][0][c], acc[0][1][c]), fmaxf(acc[1][0][c], acc[1][1][c]));
+                sm[G::S_P2 + pos * G::C2 + 4 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 4 * q + c], 0.f);  // (h,w,c) flatten
+            }
+        }
+        __syncthreads();
+        // ---- fc1: 8 k-slices x 30 float4 columns, weights streamed from L2 with 128-bit loads
+        if (tid < G::KSL * (G::F1 / 4)) {
+            const int n4 = tid % (G::F1 / 4), ks = tid / (G::F1 / 4);
+            constexpr int KL = G::FEAT / G::KSL;
+            const float4* wp = reinterpret_cast<const float4*>(W + L2.w_off) + (size_t)(ks * KL) * (G::F1 / 4) + n4;
+            const float* xp = sm + G::S_P2 + ks * KL;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 10
+            for (int k = 0; k < KL; k++) {
+                const float4 w = __ldg(wp + (size_t)k * (G::F1 / 4));
+                const float x = xp[k];
+                a.x = fmaf(x, w.x, a.x); a.y = fmaf(x, w.y, a.y); a.z = fmaf(x, w.z, a.z); a.w = fmaf(x, w.w, a.w);
+            }
+            *reinterpret_cast<float4*>(sm + G::S_PART + ks * G::F1 + 4 * n4) = a;
+        }
+        __syncthreads();
+        if (tid < G::F1) {
+            float v = __ldg(W + L2.b_off + tid);
+#pragma unroll
+            for (int ks = 0; ks < G::KSL; ks++) v += sm[G::S_PART + ks * G::F1 + tid];
+            sm[G::S_H1 + tid] = fmaxf(v, 0.f);
+        }
+        __syncthreads();
+        // ---- fc2: 3 k-slices x 84 outputs
+        if (tid < 3 * G::F2) {
+            const int j = tid % G::F2, ks = tid / G::F2;
+            const float* wp = W + L3.w_off + (size_t)(ks * 40) * G::F2 + j;
+            float a = 0.f;
+#pragma unroll 8
+            for (int k = 0; k < 40; k++) a = fmaf(sm[G::S_H1 + ks * 40 + k], __ldg(wp + (size_t)k * G::F2), a);
+            sm[G::S_H2 + ks * G::F2 + j] = a;
+        }
+        __syncthreads();
+        if (tid < G::F2) {
+            const float v = sm[G::S_H2 + tid] + sm[G::S_H2 + G::F2 + tid] + sm[G::S_H2 + 2 * G::F2 + tid] + __ldg(W + L3.b_off + tid);
+            sm[G::S_H1 + tid] = fmaxf(v, 0.f);  // h2 reuses the h1 area (fc2 has finished reading it)
+        }
+        __syncthreads();
+        // ---- fc3 + softmax / argmax: warp 0, lane = class
+        if (tid < 32) {
+            float x = -INFINITY;
+            if (tid < G::F3) {
+                float a = __ldg(W + L4.b_off + tid);
+                const float* wp = W + L4.w_off + tid;
+#pragma unroll 4
+                for (int k = 0; k < G::F2; k++) a = fmaf(sm[G::S_H1 + k], __ldg(wp + (size_t)k * G::F3), a);
+                x = a;
+            }
+            float mx = x;
+            int am = tid;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ox = __shfl_xor_sync(0xffffffffu, mx, o);
+                const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+                if (ox > mx || (ox == mx && oa < am)) { mx = ox; am = oa; }
+            }
+            const float e = tid < G::F3 ? expf(x - mx) : 0.f;
+            float s = e;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (tid < G::F3) {
+                probs[(size_t)img * G::F3 + tid] = e / s;
+                if (logits) logits[(size_t)img * G::F3 + tid] = x;
+            }
+            if (tid == 0 && argmax) argmax[img] = am;
+        }
+    }
+}
+
+template <typename G>
+int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected, const int32_t* d_list,
+                 const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, cudaStream_t st) {
+    static bool configured[64] = {};
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    const int smem = G::S_TOTAL * (int)sizeof(float);
+    if (!configured[dev & 63]) {
+        cudaError_t e = cudaFuncSetAttribute(guard_fp32_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return (int)e;
+        configured[dev & 63] = true;
+    }
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int per_sm = max(1, min(6, (200 * 1024) / smem));
+    const int grid = max(1, min(expected, sms * per_sm));
+    guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, d_list, d_count, cap, d_probs, d_logits, d_argmax);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace
+
+// Re-runs the images d_list[0 .. *d_count) in fp32 and overwrites their rows. preset: 0 mnist-lenet5, 1 cifar-lenet5.
+int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const int32_t* d_list,
+                      const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, void* stream) {
+    if (n <= 0) return 0;
+    const int expected = min(n, max(256, n / 16));  // grid sizing only; the kernel grid-strides over the real count
+    if (preset == 0)
+        return launch_guard<GNet<28, 28, 1>>(m, d_in, n, expected, d_list, d_count, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
+    return launch_guard<GNet<32, 32, 3>>(m, d_in, n, expected, d_list, d_count, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
+}
+
+}  // namespace sib
