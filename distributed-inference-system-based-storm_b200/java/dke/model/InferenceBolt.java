@@ -1,0 +1,121 @@
+package dke.model;
+
+import org.apache.storm.task.OutputCollector;
+import org.apache.storm.task.TopologyContext;
+import org.apache.storm.topology.OutputFieldsDeclarer;
+import org.apache.storm.topology.base.BaseRichBolt;
+import org.apache.storm.tuple.Fields;
+import org.apache.storm.tuple.Tuple;
+import org.apache.storm.tuple.Values;
+
+import java.io.ByteArrayOutputStream;
+import java.io.InputStream;
+import java.nio.charset.StandardCharsets;
+import java.util.ArrayDeque;
+import java.util.Map;
+
+/**
+ * Drop-in for the reference's dke.model.InferenceBolt: same package, class name, no-arg constructor, BaseRichBolt
+ * methods and output field ("message"), so MainTopology.java:54,62 needs no change. All heavy state is created in
+ * prepare(). NOT COMPILED here (no JDK/Storm jars on the boxes); the same logic is exercised through its C++ mirror
+ * csrc/sib_bolt.cpp by tests/test_bolt_contract.py.
+ */
+public class InferenceBolt extends BaseRichBolt {
+    private transient OutputCollector collector;
+    private transient long engine;
+    private transient Thread completion;
+    private transient volatile boolean stop;
+    private transient long seq;
+    /** arrival order == emit order; a null-message entry is a tuple whose JSON did not parse */
+    private transient ArrayDeque<Object[]> fifo;   // {Tuple, Boolean nullMsg}
+
+    private static int conf(Map m, String k, int d) { Object v = m.get(k); return v == null ? d : Integer.parseInt(v.toString()); }
+
+    @Override
+    public void prepare(Map map, TopologyContext ctx, OutputCollector outputCollector) {
+        this.collector = outputCollector;
+        this.fifo = new ArrayDeque<>();
+        byte[] blob;
+        try (InputStream in = getClass().getClassLoader().getResourceAsStream("model/model.sib")) {  // where saved_model.pb lived
+            ByteArrayOutputStream bo = new ByteArrayOutputStream();
+            byte[] buf = new byte[1 << 16];
+            for (int n; (n = in.read(buf)) > 0; ) bo.write(buf, 0, n);
+            blob = bo.toByteArray();
+        } catch (Exception e) { throw new RuntimeException("model/model.sib missing from the jar", e); }
+        String p = String.valueOf(map.getOrDefault("sib.precision", "fp16"));
+        int prec = p.equals("fp32") ? 2 : p.equals("bf16") ? 1 : 0;
+        int[] cfg = { conf(map, "sib.device", -1), ctx.getThisTaskIndex(), conf(map, "sib.max.batch", 0),
+                      conf(map, "sib.deadline.us", 0), prec, conf(map, "sib.slots", 0), conf(map, "sib.guard", 1) };
+        engine = NativeInfer.open(blob, cfg, 0f);
+        if (engine == 0) throw new RuntimeException("InferenceBolt.prepare: " + NativeInfer.lastError());
+        completion = new Thread(this::completionLoop, "sib-completion");
+        completion.setDaemon(true);
+        completion.start();
+    }
+
+    @Override
+    public void execute(Tuple tuple) {
+        byte[] utf8 = tuple.getString(0).getBytes(StandardCharsets.UTF_8);
+        Object[] slot = { tuple, Boolean.FALSE };
+        synchronized (fifo) { fifo.addLast(slot); fifo.notifyAll(); }   // reserve the emit position first
+        for (;;) {
+            int rc = NativeInfer.submitJson(engine, seq, utf8);
+            if (rc > 0) { seq++; return; }
+            if (rc == -1) { synchronized (fifo) { slot[1] = Boolean.TRUE; fifo.notifyAll(); } return; }  // emit null, ack
+            if (rc == -4) { Thread.yield(); continue; }                                               // ring full
+            synchronized (fifo) { fifo.removeLast(); }
+            throw new IllegalArgumentException(NativeInfer.lastError());   // what Tensor.create / copyTo threw
+        }
+    }
+
+    private void emitLeadingNulls() {   // caller holds fifo's monitor
+        while (!fifo.isEmpty() && (Boolean) fifo.peekFirst()[1]) {
+            Tuple t = (Tuple) fifo.pollFirst()[0];
+            synchronized (collector) { collector.emit(new Values((String) null)); collector.ack(t); }
+        }
+    }
+
+    private void completionLoop() {
+        long[] tags = new long[256];
+        String[] msgs = new String[256];
+        while (true) {
+            synchronized (fifo) {
+                emitLeadingNulls();
+                if (fifo.isEmpty()) {
+                    fifo.notifyAll();
+                    if (stop) return;
+                    try { fifo.wait(); } catch (InterruptedException e) { return; }
+                    continue;
+                }
+            }
+            int n = NativeInfer.pollJson(engine, tags, msgs, 2000);
+            synchronized (fifo) {
+                for (int i = 0; i < n; i++) {
+                    emitLeadingNulls();
+                    Tuple t = (Tuple) fifo.pollFirst()[0];
+                    synchronized (collector) {          // OutputCollector is not thread-safe in Storm 1.x (KafkaBolt.java:133)
+                        collector.emit(new Values(msgs[i]));
+                        collector.ack(t);
+                    }
+                }
+            }
+        }
+    }
+
+    @Override
+    public void cleanup() {
+        NativeInfer.flush(engine);
+        synchronized (fifo) {
+            fifo.notifyAll();
+            while (!fifo.isEmpty()) { try { fifo.wait(10); } catch (InterruptedException e) { break; } }
+            stop = true;
+            fifo.notifyAll();
+        }
+        NativeInfer.close(engine);
+    }
+
+    @Override
+    public void declareOutputFields(OutputFieldsDeclarer declarer) {
+        declarer.declare(new Fields("message"));
+    }
+}

@@ -1,0 +1,22 @@
+package dke.model;
+
+/**
+ * JNI face of libsib.so (include/sib.h). One long handle = one sib_engine.
+ * NOT COMPILED in this repository's CI: there is no JDK on the build or GPU boxes. Every method maps 1:1 to a
+ * C entry point; csrc/sib_jni.cpp holds the Java_dke_model_NativeInfer_* shims (built when jni.h is present).
+ */
+public final class NativeInfer {
+    static { System.loadLibrary("sib"); }
+
+    private NativeInfer() {}
+
+    /** sib_engine_open. cfg = {device, taskIndex, maxBatch, deadlineUs, precision, nSlots, guard}; returns handle. */
+    public static native long open(byte[] modelBlob, int[] cfg, float guardTau);
+    public static native void close(long engine);
+    /** sib_submit_json on the tuple's UTF-8 bytes: returns N (>0), or SIB_EJSON(-1) / SIB_ESHAPE(-2) / SIB_EAGAIN(-4). */
+    public static native int submitJson(long engine, long tag, byte[] utf8);
+    public static native void flush(long engine);
+    /** sib_poll + sib_format_json: fills tags[] and messages[] (null message = failed batch); returns count. */
+    public static native int pollJson(long engine, long[] tags, String[] messages, int timeoutUs);
+    public static native String lastError();
+}
