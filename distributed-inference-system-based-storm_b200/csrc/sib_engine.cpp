@@ -561,3 +561,12 @@ extern "C" long sib_debug_stage_dump(sib_engine* e, const float* x, int n, float
     if (r || ce != cudaSuccess) { set_error(std::string("stage dump: ") + cudaGetErrorString(r ? (cudaError_t)r : ce)); return SIB_ECUDA; }
     return need;
 }
+
+namespace sib {
+bool engine_view(sib_engine* e, EngineView* out) {
+    if (!e || !out) return false;
+    out->device = e->device; out->precision = e->cfg.precision; out->guard = e->cfg.guard; out->tau = e->cfg.guard_tau;
+    out->preset = e->model.preset; out->tc = &e->tc; out->dm = &e->dm;
+    return true;
+}
+}  // namespace sib

@@ -74,6 +74,15 @@ size_t tc_debug_floats(int preset);
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
                       GuardScratch* guard, float tau, float* d_dbg, void* stream);
 
+// Read-only view of an open engine for translation units that add entry points next to sib_engine.cpp.
+struct EngineView {
+    int device = 0, precision = 0, guard = 0, preset = -1;
+    float tau = 0.f;
+    const TcWeights* tc = nullptr;
+    const DeviceModel* dm = nullptr;
+};
+bool engine_view(sib_engine* e, EngineView* out);
+
 // fp32 recompute of the listed images, one image per CTA (sib_kernels_guard.cu). LeNet-5 presets only.
 int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const int32_t* d_list,
                       const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, void* stream);

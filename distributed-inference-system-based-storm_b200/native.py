@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libsib.so")
 
 OK, EJSON, ESHAPE, ECAP, EAGAIN, EINVAL, ECUDA, ECLOSED = 0, -1, -2, -3, -4, -5, -6, -7
 PREC_FP16, PREC_BF16, PREC_FP32 = 0, 1, 2
+STATIC_MAX_IMAGES = 16384
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(f"{LIB_PATH} is not built: run `python __graft_entry__.py build` (nvcc, sm_100a). "
@@ -59,6 +60,7 @@ SYMBOLS = {
     "sib_stats_get": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "sib_forward_sync": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sib_forward_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "sib_forward_device_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sib_debug_stage_dump": (C.c_long, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_long]),
     "sib_json_decode": (C.c_long, [C.c_char_p, C.c_size_t, C.c_void_p, C.c_long, C.POINTER(C.c_int64)]),
     "sib_json_encode": (C.c_long, [C.c_void_p, C.c_long, C.c_int, C.c_char_p, C.c_size_t]),
@@ -228,6 +230,11 @@ class Engine:
         if rc:
             raise SibError(rc, "sib_forward_sync")
         return probs, logits, argmax
+
+    def forward_device_static(self, d_in: int, n: int, d_probs: int, d_logits: int = 0, d_argmax: int = 0, stream: int = 0):
+        """sib_forward_device_static: guard scratch from the library's static device array; returns the C return code."""
+        return int(lib.sib_forward_device_static(self._h, C.c_void_p(d_in), n, C.c_void_p(d_probs), C.c_void_p(d_logits or None),
+                                                 C.c_void_p(d_argmax or None), C.c_void_p(stream or None)))
 
     def stage_dump(self, x: np.ndarray) -> np.ndarray:
         x = np.ascontiguousarray(x, np.float32)

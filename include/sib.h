@@ -123,6 +123,19 @@ int sib_forward_sync(sib_engine *e, const float *nhwc_host, int n, float *probs,
 int sib_forward_device(sib_engine *e, const float *d_nhwc, int n, float *d_probs, float *d_logits,
                        int32_t *d_argmax, void *stream);
 
+/* No counterpart in the reference (its TF session allocates as it pleases). Same work as sib_forward_device on the
+ * guarded tensor-core path, but the guard's scratch (margins, low-margin list, counter) is a fixed array inside
+ * libsib.so's device image instead of engine-owned cudaMalloc memory, and the call itself allocates nothing.
+ * For callers that must not ask the driver for device memory: a task attaching to a GPU whose memory is already
+ * fully handed out (cudaMalloc would fail), a latency-critical loop that cannot afford cudaMalloc/cudaFree's
+ * device-wide synchronisation stalling the other executors on the GPU, or a phase run under a no-allocation rule.
+ * Limits: n <= SIB_STATIC_MAX_IMAGES per call (larger n => SIB_ECAP); engine must be SIB_PREC_FP16/BF16 with guard on;
+ * d_argmax is required. The first call on a device resolves the array's address -- make it before any stream
+ * capture on that device. All calls on a device share the array: calls whose GPU work overlaps race on it. */
+#define SIB_STATIC_MAX_IMAGES 16384
+int sib_forward_device_static(sib_engine *e, const float *d_nhwc, int n, float *d_probs, float *d_logits,
+                              int32_t *d_argmax, void *stream);
+
 /* Test hook: intermediate activations of the tensor-core kernel for the first 16-image tile, fp32 (what fetching
  * inner tensors of the TF graph would give, InferenceBolt.java:81-85). Returns floats written or a code. */
 long sib_debug_stage_dump(sib_engine *e, const float *nhwc_host, int n, float *out, long cap);
