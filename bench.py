@@ -43,10 +43,11 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--preset", default="cifar-lenet5")
-    ap.add_argument("--batch", type=int, default=16384, help="images per step per GPU")
+    ap.add_argument("--batch", type=int, default=65536, help="images per step per GPU")
     ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "fp16", "bf16"])
     ap.add_argument("--no-guard", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
+    ap.add_argument("--submit-threads", type=int, default=0, help="host threads feeding one GPU in the e2e leg")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     return ap.parse_args()
@@ -232,30 +233,71 @@ def run_ours(args):
     checksum = float(d_probs.sum().item())  # every row sums to 1: B
     assert abs(checksum - B) < 1e-2 * B, checksum
 
-    # ---- T1: host buffers through the C ABI (submit chunks of 1024 images; engine batches to B)
+    # ---- dominant kernel alone (forward_tc_kernel): same batches through a guard-off engine, CUDA events on the
+    # launching stream. The step time above also holds the guard's recompute kernel; the roofline is the kernel's.
+    tc_ms = None
+    if prec != native.PREC_FP32 and not args.no_guard:
+        eng0 = native.Engine(blob, device=dev, task_index=rank, max_batch=B, precision=prec, n_slots=2, guard=False)
+        with torch.cuda.stream(stream):
+            for i in range(args.warmup):
+                eng0.forward_device(d_in[i % R].data_ptr(), B, d_probs.data_ptr(), 0, d_argmax.data_ptr(), stream.cuda_stream)
+            ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+            torch.cuda.synchronize()
+            ev2[0].record(stream)
+            for i in range(args.steps):
+                eng0.forward_device(d_in[i % R].data_ptr(), B, d_probs.data_ptr(), 0, d_argmax.data_ptr(), stream.cuda_stream)
+                ev2[i + 1].record(stream)
+            torch.cuda.synchronize()
+        tc_ms = statistics.median(ev2[i].elapsed_time(ev2[i + 1]) for i in range(args.steps))
+        eng0.close()
+
+    # ---- T1: host buffers through the C ABI. Like a Storm worker with several executors feeding one GPU, a few
+    # host threads submit chunks of fp32 images (sib_submit_f32 copies them into the pinned slot outside the engine
+    # lock; ctypes releases the GIL for the call) while this thread polls results.
     e2e = None
     if not args.skip_e2e:
+        import threading
         chunk = min(1024, B)
         per_step = B // chunk
+        cores = os.cpu_count() or 8
+        want_thr = args.submit_threads if args.submit_threads > 0 else min(8, max(1, cores // max(1, world) - 1))
+        n_thr = max(1, min(want_thr, per_step))
+
         def e2e_steps(n_steps, first):
+            total = n_steps * per_step * chunk
+            err = []
+
+            def worker(t):
+                try:
+                    for s_ in range(n_steps):
+                        h = host_batches[(first + s_) % R]
+                        for c in range(t, per_step, n_thr):
+                            part = h[c * chunk:(c + 1) * chunk]
+                            while True:
+                                rc = eng.submit_f32(s_ * per_step + c, part)
+                                if rc == native.EAGAIN:
+                                    time.sleep(0.00005)
+                                    continue
+                                if rc < 0:
+                                    raise native.SibError(rc, "sib_submit_f32")
+                                break
+                except Exception as ex:  # noqa: BLE001
+                    err.append(ex)
+
+            ths = [threading.Thread(target=worker, args=(t,)) for t in range(n_thr)]
+            for t in ths:
+                t.start()
             got = 0
-            for s in range(n_steps):
-                h = host_batches[(first + s) % R]
-                for c in range(per_step):
-                    part = h[c * chunk:(c + 1) * chunk]
-                    while True:
-                        rc = eng.submit_f32(s * per_step + c, part)
-                        if rc == native.EAGAIN:
-                            got += _poll_count(eng, 200)
-                            continue
-                        if rc < 0:
-                            raise native.SibError(rc, "sib_submit_f32")
-                        break
-                got += _poll_count(eng, 0)
-            eng.flush()
-            while got < n_steps * B:
-                got += _poll_count(eng, -1)
+            while got < total and not err:
+                got += _poll_count(eng, 2000)
+                if not any(t.is_alive() for t in ths):
+                    eng.flush()
+            for t in ths:
+                t.join()
+            if err:
+                raise err[0]
             return got
+
         e2e_steps(max(1, min(args.warmup, 3)), 0)
         st0 = eng.stats()
         torch.cuda.synchronize()
@@ -263,14 +305,15 @@ def run_ours(args):
             dist.barrier()
         t_a = time.perf_counter()
         n_e2e = max(2, min(args.steps, 10))
-        e2e_steps(n_e2e, 1)
+        done = e2e_steps(n_e2e, 1)
         torch.cuda.synchronize()
         t_b = time.perf_counter()
         if world > 1:
             dist.barrier()
         st1 = eng.stats()
-        u2, s2 = sharding.aggregate(B * n_e2e, t_b - t_a, dist if world > 1 else None)
-        e2e = {"value": u2 / s2, "unit": "images/s", "level": "T1: sib_submit_f32/sib_poll, host fp32 buffers",
+        u2, s2 = sharding.aggregate(done, t_b - t_a, dist if world > 1 else None)
+        e2e = {"value": u2 / s2, "unit": "images/s",
+               "level": f"T1: sib_submit_f32/sib_poll, host fp32 buffers, {n_thr} submitting threads per GPU",
                "h2d_bytes_per_step": (st1.h2d_bytes - st0.h2d_bytes) // n_e2e,
                "d2h_bytes_per_step": (st1.d2h_bytes - st0.d2h_bytes) // n_e2e, "steps": n_e2e}
 
@@ -289,7 +332,8 @@ def run_ours(args):
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
     bpi = model.bytes_per_image()
-    k_ms = statistics.median(step_ms)  # one step = one launch of the forward kernel (+ guard launch)
+    step_med = statistics.median(step_ms)   # one step = forward kernel launch (+ the guard's recompute launch)
+    k_ms = tc_ms if tc_ms is not None else step_med
     achieved = B * bpi / (k_ms * 1e-3) * 1e-9
     traffic = None
     tr = os.path.join(ROOT, "profiles", "traffic.json")
@@ -307,7 +351,10 @@ def run_ours(args):
         "e2e": e2e, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                     "kernel_ms": k_ms, "algorithmic_bytes_per_image": bpi, "images_per_launch": B,
+                     "kernel": "forward_fp32_kernel" if prec_name == "fp32" else "forward_tc_kernel",
+                     "kernel_ms": k_ms, "step_ms": step_med,
+                     "guard_kernel_ms": (step_med - tc_ms) if tc_ms is not None else 0.0,
+                     "algorithmic_bytes_per_image": bpi, "images_per_launch": B,
                      "flops_per_image": model.flops_per_image()},
         "clocks": clocks, "guard_recomputed_images": int(guard_n),
     }

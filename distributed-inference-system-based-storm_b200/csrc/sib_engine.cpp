@@ -49,7 +49,10 @@ struct DevBufs {  // one forward's worth of device memory
 };
 
 struct Slot {
-    enum State { FREE, FILLING, INFLIGHT, READY, HANDED };
+    // FILLING: accepting tuples. SEALED: closed to new tuples and queued for launch, but some submitter is still
+    // copying its images in (writers > 0). INFLIGHT: copies and kernels issued. READY: results in h_probs.
+    // HANDED: results given out by sib_poll, slot recycled at the next poll.
+    enum State { FREE, FILLING, SEALED, INFLIGHT, READY, HANDED };
     State state = FREE;
     float* h_in = nullptr;       // pinned, max_batch x img
     float* h_probs = nullptr;    // pinned, max_batch x ncls
@@ -62,6 +65,8 @@ struct Slot {
     size_t next_entry = 0;
     int images = 0;
     int status = SIB_OK;
+    int writers = 0;       // submitters that reserved room and are copying outside the lock
+    int flush_reason = 0;  // why it was sealed: 0 size, 1 deadline, 2 explicit
     Clock::time_point first_ts;
 };
 
@@ -78,7 +83,7 @@ struct sib_engine {
     TcWeights tc{};
     std::vector<Slot> slots;
     int filling = -1;
-    std::deque<int> fifo;  // launched slots, submission order
+    std::deque<int> fifo;  // sealed/launched slots, submission order
     std::mutex mu;
     std::condition_variable cv;
     std::thread deadline_thread;
@@ -95,7 +100,8 @@ struct sib_engine {
     void free_slot(Slot& s);
     int run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax, GuardScratch* g,
                     cudaStream_t st);
-    int launch_locked(int si, int reason);
+    int seal_locked(int si, int reason);  // stop filling; launches at once unless a writer is still copying
+    int launch_locked(int si);
     void deadline_main();
 };
 
@@ -170,8 +176,20 @@ int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_l
     return SIB_OK;
 }
 
-int sib_engine::launch_locked(int si, int reason) {
+int sib_engine::seal_locked(int si, int reason) {
     Slot& s = slots[si];
+    s.state = Slot::SEALED;
+    s.flush_reason = reason;
+    s.next_entry = 0;
+    fifo.push_back(si);  // result order is fixed here, at seal time
+    if (filling == si) filling = -1;
+    if (s.writers == 0) return launch_locked(si);
+    return SIB_OK;  // the last writer launches it
+}
+
+int sib_engine::launch_locked(int si) {
+    Slot& s = slots[si];
+    const int reason = s.flush_reason;
     cudaSetDevice(device);
     const size_t nc = model.n_classes;
     int rc = SIB_OK;
@@ -194,9 +212,6 @@ int sib_engine::launch_locked(int si, int reason) {
     chk(cudaEventRecord(s.done, s.stream), "event record");
     s.status = rc;
     s.state = Slot::INFLIGHT;
-    s.next_entry = 0;
-    fifo.push_back(si);
-    if (filling == si) filling = -1;
     stats.batches++;
     stats.h2d_bytes += in_bytes;
     stats.d2h_bytes += d2h;
@@ -221,7 +236,7 @@ void sib_engine::deadline_main() {
         const int si = filling;
         const auto due = slots[si].first_ts + std::chrono::microseconds(cfg.deadline_us);
         if (Clock::now() >= due) {
-            launch_locked(si, 1);
+            seal_locked(si, 1);
             continue;
         }
         cv.wait_until(lk, due);
@@ -317,9 +332,15 @@ extern "C" int sib_engine_close(sib_engine* e) {
     if (!e) return SIB_EINVAL;
     {
         std::unique_lock<std::mutex> lk(e->mu);
-        if (e->filling >= 0 && e->slots[e->filling].images > 0) e->launch_locked(e->filling, 2);
+        if (e->filling >= 0 && e->slots[e->filling].images > 0) e->seal_locked(e->filling, 2);
         e->closing = true;
         e->cv.notify_all();
+        // submitters still copying into sealed slots finish first (they launch the slot themselves)
+        e->cv.wait(lk, [e] {
+            for (auto& s : e->slots)
+                if (s.writers > 0) return false;
+            return true;
+        });
     }
     if (e->deadline_thread.joinable()) e->deadline_thread.join();
     cudaSetDevice(e->device);
@@ -348,12 +369,13 @@ extern "C" int sib_engine_info(sib_engine* e, sib_model_info* out, sib_config* e
 // Finds (or starts) the slot to append n images to. Returns slot index or a negative code. Caller holds mu.
 static int slot_for(sib_engine* e, int n) {
     if (n > e->cfg.max_batch) { set_error("tuple holds more images than max_batch"); return SIB_ECAP; }
-    if (e->filling >= 0 && e->slots[e->filling].images + n > e->cfg.max_batch) e->launch_locked(e->filling, 0);
+    if (e->filling >= 0 && e->slots[e->filling].images + n > e->cfg.max_batch) e->seal_locked(e->filling, 0);
     if (e->filling < 0) {
         for (size_t i = 0; i < e->slots.size(); i++) {
             if (e->slots[i].state == Slot::FREE) {
                 Slot& s = e->slots[i];
                 s.state = Slot::FILLING;
+                s.writers = 0;
                 s.images = 0;
                 s.entries.clear();
                 s.next_entry = 0;
@@ -367,67 +389,112 @@ static int slot_for(sib_engine* e, int n) {
     return e->filling;
 }
 
-static void appended(sib_engine* e, int si, uint64_t tag, int n) {
+// Reserves room for n images in slot si and fixes the tuple's place in the result order. The caller copies its
+// images to the returned offset WITHOUT the lock (so several executor threads fill one batch in parallel), then
+// calls written(). Caller holds mu.
+static int reserve(sib_engine* e, int si, uint64_t tag, int n) {
     Slot& s = e->slots[si];
+    const int off = s.images;
     if (s.images == 0) {
         s.first_ts = Clock::now();
         e->cv.notify_all();  // arm the deadline thread
     }
-    s.entries.push_back(Entry{tag, n, s.images});
+    s.entries.push_back(Entry{tag, n, off});
     s.images += n;
+    s.writers++;
     e->stats.tuples++;
     e->stats.images += (uint64_t)n;
-    if (s.images >= e->cfg.max_batch) e->launch_locked(si, 0);
+    if (s.images >= e->cfg.max_batch) e->seal_locked(si, 0);  // full: sealed now, launched when the copies are in
+    return off;
+}
+
+static void written(sib_engine* e, int si) {
+    std::unique_lock<std::mutex> lk(e->mu);
+    Slot& s = e->slots[si];
+    if (--s.writers == 0) {
+        if (s.state == Slot::SEALED) e->launch_locked(si);
+        e->cv.notify_all();
+    }
 }
 
 extern "C" int sib_submit_f32(sib_engine* e, uint64_t tag, const float* nhwc, int n) {
     if (!e || !nhwc || n <= 0) return SIB_EINVAL;
-    std::unique_lock<std::mutex> lk(e->mu);
-    if (e->closing) return SIB_ECLOSED;
-    int si = slot_for(e, n);
-    if (si < 0) return si;
-    Slot& s = e->slots[si];
-    std::memcpy(s.h_in + (size_t)s.images * e->model.img_elems, nhwc, (size_t)n * e->model.img_elems * sizeof(float));
-    appended(e, si, tag, n);
+    int si, off;
+    {
+        std::unique_lock<std::mutex> lk(e->mu);
+        if (e->closing) return SIB_ECLOSED;
+        si = slot_for(e, n);
+        if (si < 0) return si;
+        off = reserve(e, si, tag, n);
+    }
+    const size_t img = e->model.img_elems;
+    std::memcpy(e->slots[si].h_in + (size_t)off * img, nhwc, (size_t)n * img * sizeof(float));
+    written(e, si);
     return n;
 }
 
 extern "C" int sib_submit_json(sib_engine* e, uint64_t tag, const char* utf8, size_t len) {
     if (!e || !utf8) return SIB_EINVAL;
-    std::unique_lock<std::mutex> lk(e->mu);
-    if (e->closing) return SIB_ECLOSED;
     const ModelDesc& m = e->model;
-    for (int attempt = 0; attempt < 2; attempt++) {
-        int si = slot_for(e, 1);
+    const size_t img = m.img_elems;
+    // The usual tuple carries one instance (InferenceBolt.java:86 hard-wires [1][10]): reserve one image and decode
+    // the text straight into the pinned slot, outside the lock. A tuple with more instances does not fit that
+    // reservation; it is decoded into a thread-local buffer and copied in like sib_submit_f32 does.
+    int si, off;
+    {
+        std::unique_lock<std::mutex> lk(e->mu);
+        if (e->closing) return SIB_ECLOSED;
+        si = slot_for(e, 1);
         if (si < 0) return si;
-        Slot& s = e->slots[si];
-        const long room = (long)(e->cfg.max_batch - s.images) * (long)m.img_elems;
-        int64_t dims[4];
-        long nf = json_decode(utf8, len, s.h_in + (size_t)s.images * m.img_elems, room, dims);
-        if (nf == SIB_EJSON) { set_error("malformed instances JSON"); return SIB_EJSON; }
-        if (nf == SIB_ESHAPE) { set_error("instances is not a rectangular rank-4 array"); return SIB_ESHAPE; }
-        if (nf != SIB_ECAP && nf < 0) return (int)nf;
+        off = reserve(e, si, tag, 1);
+    }
+    Slot& s = e->slots[si];
+    int64_t dims[4] = {0, 0, 0, 0};
+    long nf = json_decode(utf8, len, s.h_in + (size_t)off * img, (long)img, dims);
+    int rc = 1;
+    if (nf == SIB_EJSON) { set_error("malformed instances JSON"); rc = SIB_EJSON; }
+    else if (nf == SIB_ESHAPE) { set_error("instances is not a rectangular rank-4 array"); rc = SIB_ESHAPE; }
+    else if (nf == SIB_ECAP || nf > 0) {
         if (dims[1] != m.in_h || dims[2] != m.in_w || dims[3] != m.in_c) {
             set_error("instances HxWxC does not match the model input");
-            return SIB_ESHAPE;
+            rc = SIB_ESHAPE;
+        } else if (dims[0] > e->cfg.max_batch) {
+            set_error("tuple holds more images than max_batch");
+            rc = SIB_ECAP;
+        } else if (dims[0] != 1) {
+            rc = 0;  // N > 1: second path below
         }
-        if (dims[0] > e->cfg.max_batch) { set_error("tuple holds more images than max_batch"); return SIB_ECAP; }
-        if (nf == SIB_ECAP) {
-            // did not fit behind the tuples already queued: launch those and decode again into a fresh slot
-            if (s.images == 0) return SIB_ECAP;
-            e->launch_locked(si, 0);
-            continue;
-        }
-        appended(e, si, tag, (int)dims[0]);
-        return (int)dims[0];
+    } else {
+        rc = (int)nf;
     }
-    return SIB_EAGAIN;
+    if (rc == 1) {
+        written(e, si);
+        return 1;
+    }
+    // The reservation is not used after all: turn it into an empty entry (its image row is computed and dropped).
+    {
+        std::unique_lock<std::mutex> lk(e->mu);
+        for (auto& en : s.entries)
+            if (en.offset == off && en.tag == tag && en.n == 1) { en.n = 0; break; }
+        std::memset(s.h_in + (size_t)off * img, 0, img * sizeof(float));
+        e->stats.tuples--;
+        e->stats.images--;
+    }
+    written(e, si);
+    if (rc < 0) return rc;
+    static thread_local std::vector<float> tmp;
+    const size_t need = (size_t)dims[0] * img;
+    if (tmp.size() < need) tmp.resize(need);
+    nf = json_decode(utf8, len, tmp.data(), (long)need, dims);
+    if (nf < 0) return (int)nf;
+    int r = sib_submit_f32(e, tag, tmp.data(), (int)dims[0]);
+    return r;
 }
 
 extern "C" int sib_flush(sib_engine* e) {
     if (!e) return SIB_EINVAL;
     std::unique_lock<std::mutex> lk(e->mu);
-    if (e->filling >= 0 && e->slots[e->filling].images > 0) return e->launch_locked(e->filling, 2);
+    if (e->filling >= 0 && e->slots[e->filling].images > 0) return e->seal_locked(e->filling, 2);
     return SIB_OK;
 }
 
@@ -443,6 +510,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
     for (;;) {
         while (got < max && !e->fifo.empty()) {
             Slot& s = e->slots[e->fifo.front()];
+            if (s.state == Slot::SEALED) break;  // a submitter is still copying into it
             if (s.state == Slot::INFLIGHT) {
                 cudaError_t q = cudaEventQuery(s.done);
                 if (q == cudaErrorNotReady) break;
@@ -455,6 +523,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
             }
             while (got < max && s.next_entry < s.entries.size()) {
                 const Entry& en = s.entries[s.next_entry++];
+                if (en.n == 0) continue;  // reservation that was given back (see sib_submit_json)
                 sib_result& r = out[got++];
                 r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status; r.reserved = 0;
                 r.probs = s.h_probs + (size_t)en.offset * nc;
@@ -471,7 +540,10 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
         const bool pending = !e->fifo.empty() || (e->filling >= 0 && e->slots[e->filling].images > 0);
         if (!pending) break;
         if (timeout_us > 0 && Clock::now() >= t_end) break;
-        if (!e->fifo.empty()) {
+        if (!e->fifo.empty() && e->slots[e->fifo.front()].state == Slot::SEALED) {
+            if (timeout_us < 0) e->cv.wait(lk);
+            else e->cv.wait_until(lk, t_end);
+        } else if (!e->fifo.empty()) {
             // wait for the oldest batch without holding the lock
             cudaEvent_t ev = e->slots[e->fifo.front()].done;
             lk.unlock();
