@@ -65,6 +65,8 @@ struct Slot {
     size_t next_entry = 0;
     int images = 0;
     int status = SIB_OK;
+    std::vector<std::pair<int, int>> staged;  // (offset, n) image ranges that sit in h_in and need the H2D at launch
+    size_t direct_bytes = 0;                  // bytes already sent device-ward straight from caller-pinned memory
     int writers = 0;       // submitters that reserved room and are copying outside the lock
     int flush_reason = 0;  // why it was sealed: 0 size, 1 deadline, 2 explicit
     Clock::time_point first_ts;
@@ -199,8 +201,13 @@ int sib_engine::launch_locked(int si) {
             rc = SIB_ECUDA;
         }
     };
-    const size_t in_bytes = (size_t)s.images * model.img_elems * sizeof(float);
-    chk(cudaMemcpyAsync(s.dev.d_in, s.h_in, in_bytes, cudaMemcpyHostToDevice, s.stream), "H2D");
+    const size_t img_bytes = (size_t)model.img_elems * sizeof(float);
+    size_t in_bytes = s.direct_bytes;
+    for (auto& r : s.staged) {  // one copy per contiguous staged range (normally exactly one)
+        chk(cudaMemcpyAsync(s.dev.d_in + (size_t)r.first * model.img_elems, s.h_in + (size_t)r.first * model.img_elems,
+                            (size_t)r.second * img_bytes, cudaMemcpyHostToDevice, s.stream), "H2D");
+        in_bytes += (size_t)r.second * img_bytes;
+    }
     if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
     chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)s.images * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream), "D2H probs");
     chk(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)s.images * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H argmax");
@@ -375,6 +382,8 @@ static int slot_for(sib_engine* e, int n) {
             if (e->slots[i].state == Slot::FREE) {
                 Slot& s = e->slots[i];
                 s.state = Slot::FILLING;
+                s.staged.clear();
+                s.direct_bytes = 0;
                 s.writers = 0;
                 s.images = 0;
                 s.entries.clear();
@@ -392,9 +401,13 @@ static int slot_for(sib_engine* e, int n) {
 // Reserves room for n images in slot si and fixes the tuple's place in the result order. The caller copies its
 // images to the returned offset WITHOUT the lock (so several executor threads fill one batch in parallel), then
 // calls written(). Caller holds mu.
-static int reserve(sib_engine* e, int si, uint64_t tag, int n) {
+static int reserve(sib_engine* e, int si, uint64_t tag, int n, bool staged = true) {
     Slot& s = e->slots[si];
     const int off = s.images;
+    if (staged) {
+        if (!s.staged.empty() && s.staged.back().first + s.staged.back().second == off) s.staged.back().second += n;
+        else s.staged.emplace_back(off, n);
+    }
     if (s.images == 0) {
         s.first_ts = Clock::now();
         e->cv.notify_all();  // arm the deadline thread
@@ -430,6 +443,27 @@ extern "C" int sib_submit_f32(sib_engine* e, uint64_t tag, const float* nhwc, in
     const size_t img = e->model.img_elems;
     std::memcpy(e->slots[si].h_in + (size_t)off * img, nhwc, (size_t)n * img * sizeof(float));
     written(e, si);
+    return n;
+}
+
+extern "C" int sib_submit_pinned(sib_engine* e, uint64_t tag, const float* pinned_nhwc, int n) {
+    if (!e || !pinned_nhwc || n <= 0) return SIB_EINVAL;
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (e->closing) return SIB_ECLOSED;
+    const int si = slot_for(e, n);
+    if (si < 0) return si;
+    Slot& s = e->slots[si];
+    const int off = s.images;
+    // No host staging: the DMA reads the caller's page-locked memory and lands in the slot's device buffer. It is
+    // enqueued before the reservation can seal the slot, so the batch's kernel is ordered after it on the stream.
+    cudaSetDevice(e->device);
+    const size_t bytes = (size_t)n * e->model.img_elems * sizeof(float);
+    cudaError_t ce = cudaMemcpyAsync(s.dev.d_in + (size_t)off * e->model.img_elems, pinned_nhwc, bytes,
+                                     cudaMemcpyHostToDevice, s.stream);
+    if (ce != cudaSuccess) { set_error(std::string("sib_submit_pinned H2D: ") + cudaGetErrorString(ce)); return SIB_ECUDA; }
+    s.direct_bytes += bytes;
+    reserve(e, si, tag, n, false);  // counts this call as a writer, so a slot that just became full is only sealed
+    if (--s.writers == 0 && s.state == Slot::SEALED) e->launch_locked(si);
     return n;
 }
 

@@ -54,6 +54,7 @@ SYMBOLS = {
     "sib_engine_info": (C.c_int, [C.c_void_p, C.POINTER(ModelInfo), C.POINTER(Config)]),
     "sib_submit_json": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_size_t]),
     "sib_submit_f32": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
+    "sib_submit_pinned": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
     "sib_poll": (C.c_int, [C.c_void_p, C.POINTER(Result), C.c_int, C.c_int]),
     "sib_flush": (C.c_int, [C.c_void_p]),
     "sib_format_json": (C.c_long, [C.POINTER(Result), C.c_char_p, C.c_size_t]),
@@ -177,6 +178,10 @@ class Engine:
         x = np.ascontiguousarray(x, np.float32)
         n = x.size // self.img_elems
         return int(lib.sib_submit_f32(self._h, tag, _p(x), n))
+
+    def submit_pinned(self, tag: int, ptr: int, n: int) -> int:
+        """ptr: address of n images of fp32 NHWC in page-locked host memory (kept alive by the caller)."""
+        return int(lib.sib_submit_pinned(self._h, tag, C.c_void_p(ptr), n))
 
     def flush(self):
         rc = lib.sib_flush(self._h)

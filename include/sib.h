@@ -98,6 +98,11 @@ int sib_submit_json(sib_engine *e, uint64_t tag, const char *utf8, size_t len);
  * before return. */
 int sib_submit_f32(sib_engine *e, uint64_t tag, const float *nhwc, int n);
 
+/* Zero-copy form of sib_submit_f32 for a caller whose fp32 NHWC already sits in page-locked host memory (a direct
+ * ByteBuffer registered with cudaHostRegister, cudaHostAlloc memory): the DMA reads the caller's buffer, nothing is
+ * staged. The buffer must stay untouched until the tuple's result has been returned by sib_poll. */
+int sib_submit_pinned(sib_engine *e, uint64_t tag, const float *pinned_nhwc, int n);
+
 /* sess.runner().feed().fetch().run() + copyTo (InferenceBolt.java:81-86), decoupled: returns up to max completed
  * tuples in submission order. timeout_us: 0 = don't wait, <0 = wait until at least one is ready or nothing is
  * pending. Returns the count. Invalidates pointers handed out by the previous poll. */

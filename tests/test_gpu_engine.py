@@ -107,3 +107,26 @@ def test_close_with_pending_work(sib, presets):
     for i in range(10):
         e.submit_f32(i, x[i])
     e.close()  # must flush, wait and free without hanging
+
+
+def test_submit_pinned_is_zero_copy_and_mixes_with_staged(sib, oracle, presets):
+    torch = pytest.importorskip("torch")
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 26, 96)
+    _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    pinned = torch.empty((96, 28, 28, 1), dtype=torch.float32, pin_memory=True)
+    pinned.numpy()[:] = x
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6) as e:
+        # tuples alternate between caller-pinned memory (DMA straight from it) and staged copies, inside one batch
+        for i in range(0, 96, 8):
+            if (i // 8) % 2 == 0:
+                assert e.submit_pinned(i, pinned.data_ptr() + i * 784 * 4, 8) == 8
+            else:
+                assert e.submit_f32(i, x[i:i + 8]) == 8
+        e.flush()
+        got = _drain(e, 12)
+        assert [t for t, *_ in got] == list(range(0, 96, 8))
+        P = np.concatenate([p for _, p, _, _ in got])
+        assert np.abs(P - pr).max() <= 1e-5
+        st = e.stats()
+        assert st.h2d_bytes == 96 * 784 * 4 and st.flush_by_size == 1
