@@ -254,3 +254,56 @@ class Engine:
                                     C.c_void_p(d_argmax or None), C.c_void_p(stream or None))
         if rc:
             raise SibError(rc, "sib_forward_device")
+
+
+# ---- open-loop load generator (include/sib_loadgen.h) -------------------------------------------------------------
+
+LG_JSON, LG_F32 = 0, 1
+
+
+class LoadgenCfg(C.Structure):
+    _fields_ = [("rate_per_s", C.c_double), ("n_tuples", C.c_int64), ("mode", C.c_int32), ("producers", C.c_int32),
+                ("poisson", C.c_int32), ("reserved", C.c_int32), ("seed", C.c_uint64)]
+
+
+class LoadgenReport(C.Structure):
+    _fields_ = [("completed", C.c_int64), ("rejected", C.c_int64), ("images", C.c_int64), ("wall_s", C.c_double),
+                ("achieved_tuples_per_s", C.c_double), ("p50_ns", C.c_int64), ("p90_ns", C.c_int64),
+                ("p99_ns", C.c_int64), ("p999_ns", C.c_int64), ("max_ns", C.c_int64), ("mean_ns", C.c_int64),
+                ("eagain_spins", C.c_int64), ("late_submits", C.c_int64)]
+
+
+LOADGEN_SYMBOLS = ["sib_loadgen_run"]
+lib.sib_loadgen_run.restype = C.c_int
+lib.sib_loadgen_run.argtypes = [C.c_void_p, C.POINTER(LoadgenCfg), C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int,
+                                C.c_void_p, C.POINTER(LoadgenReport)]
+
+
+def loadgen(engine: "Engine", payloads, rate_per_s: float, n_tuples: int, mode: int = LG_JSON, producers: int = 1,
+            poisson: bool = False, seed: int = 99, want_latencies: bool = False):
+    """payloads: list of bytes (JSON mode) or contiguous float32 ndarrays (F32 mode). -> dict report (+ latencies)."""
+    keep = []
+    ptrs = (C.c_void_p * len(payloads))()
+    lens = (C.c_size_t * len(payloads))()
+    for i, p in enumerate(payloads):
+        if isinstance(p, (bytes, bytearray)):
+            b = C.create_string_buffer(bytes(p), len(p))
+            keep.append(b)
+            ptrs[i] = C.cast(b, C.c_void_p)
+            lens[i] = len(p)
+        else:
+            a = np.ascontiguousarray(p, np.float32)
+            keep.append(a)
+            ptrs[i] = a.ctypes.data
+            lens[i] = a.nbytes
+    cfg = LoadgenCfg(rate_per_s, n_tuples, mode, producers, 1 if poisson else 0, 0, seed)
+    rep = LoadgenReport()
+    lat = np.empty(n_tuples, np.int64) if want_latencies else None
+    rc = lib.sib_loadgen_run(engine.handle, C.byref(cfg), ptrs, lens, len(payloads), _p(lat) if want_latencies else None,
+                             C.byref(rep))
+    if rc:
+        raise SibError(rc, "sib_loadgen_run")
+    out = {f: getattr(rep, f) for f, _ in LoadgenReport._fields_}
+    if want_latencies:
+        out["latencies_ns"] = lat
+    return out

@@ -53,6 +53,8 @@ def lib():
         L.sibo_run_tuples.restype = C.c_long
         L.sibo_run_tuples.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_long, C.c_int, C.c_void_p]
         L.sibo_sizeof_model.restype = C.c_size_t
+        L.sibo_latency_run.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int, C.c_int,
+                                       C.c_double, C.c_long, C.c_int, C.c_void_p]
         L.sibo_conv2d_valid.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.sibo_maxpool2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.sibo_dense.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
@@ -129,6 +131,21 @@ class Model:
         ob = C.c_long(0)
         ok = lib().sibo_run_tuples(self._m, blob, _p(offs), len(tuples), threads, C.byref(ob))
         return ok, ob.value
+
+
+def latency_run(model: "Model", payloads, rate_per_s: float, n_tuples: int, threads: int = 4, json_mode: bool = True):
+    """Open-loop latency of the CPU path (see sibo_latency_run). -> int64 ndarray of per-tuple latencies in ns."""
+    keep, ptrs, lens = [], (C.c_void_p * len(payloads))(), (C.c_size_t * len(payloads))()
+    for i, p in enumerate(payloads):
+        if isinstance(p, (bytes, bytearray)):
+            b = C.create_string_buffer(bytes(p), len(p)); keep.append(b)
+            ptrs[i] = C.cast(b, C.c_void_p); lens[i] = len(p)
+        else:
+            a = np.ascontiguousarray(p, np.float32); keep.append(a)
+            ptrs[i] = a.ctypes.data; lens[i] = a.nbytes
+    lat = np.empty(n_tuples, np.int64)
+    lib().sibo_latency_run(model._m, ptrs, lens, len(payloads), 0 if json_mode else 1, rate_per_s, n_tuples, threads, _p(lat))
+    return lat
 
 
 def json_decode(text: bytes, cap: int | None = None):

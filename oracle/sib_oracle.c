@@ -170,20 +170,24 @@ long sibo_make_preset(int preset, void *out, size_t cap) {
 
 /* ------------------------------------------------------------------ ops, fp32 (TF 1.x semantics) */
 
-/* Conv2D NHWC x HWIO, VALID, stride 1 (cross-correlation, no filter flip). One image. */
+/* Conv2D NHWC x HWIO, VALID, stride 1 (cross-correlation, no filter flip). One image.
+ * Every output is the sum over (kh, kw, ci) in that order, one fp32 multiply and one fp32 add per term; the output
+ * channel is the innermost loop only so that the compiler can vectorise over it (it does not change any sum). */
 void sibo_conv2d_valid(const float *in, int h, int w, int cin, const float *filt, int kh, int kw, int cout,
                        float *out) {
     int oh = h - kh + 1, ow = w - kw + 1;
     for (int y = 0; y < oh; y++)
-        for (int x = 0; x < ow; x++)
-            for (int co = 0; co < cout; co++) {
-                float acc = 0.0f;
-                for (int i = 0; i < kh; i++)
-                    for (int j = 0; j < kw; j++)
-                        for (int ci = 0; ci < cin; ci++)
-                            acc += in[((y + i) * w + (x + j)) * cin + ci] * filt[((i * kw + j) * cin + ci) * cout + co];
-                out[(y * ow + x) * cout + co] = acc;
-            }
+        for (int x = 0; x < ow; x++) {
+            float *acc = out + (y * ow + x) * cout;
+            for (int co = 0; co < cout; co++) acc[co] = 0.0f;
+            for (int i = 0; i < kh; i++)
+                for (int j = 0; j < kw; j++)
+                    for (int ci = 0; ci < cin; ci++) {
+                        const float v = in[((y + i) * w + (x + j)) * cin + ci];
+                        const float *wp = filt + ((i * kw + j) * cin + ci) * cout;
+                        for (int co = 0; co < cout; co++) acc[co] += v * wp[co];
+                    }
+        }
 }
 
 void sibo_bias_add(float *x, int n_pos, int c, const float *bias) {
@@ -208,12 +212,13 @@ void sibo_maxpool2(const float *in, int h, int w, int c, float *out) {
             }
 }
 
-/* MatMul [1,K] x [K,M] with W stored [in,out] */
+/* MatMul [1,K] x [K,M] with W stored [in,out]: out[j] = sum over i in order (inner loop over j vectorises) */
 void sibo_dense(const float *x, int k, const float *wt, int m, float *out) {
-    for (int j = 0; j < m; j++) {
-        float acc = 0.0f;
-        for (int i = 0; i < k; i++) acc += x[i] * wt[i * m + j];
-        out[j] = acc;
+    for (int j = 0; j < m; j++) out[j] = 0.0f;
+    for (int i = 0; i < k; i++) {
+        const float v = x[i];
+        const float *wp = wt + (size_t)i * m;
+        for (int j = 0; j < m; j++) out[j] += v * wp[j];
     }
 }
 
@@ -662,3 +667,63 @@ long sibo_run_tuples(const sibo_model *m, const char *tuples, const long *offs, 
 }
 
 size_t sibo_sizeof_model(void) { return sizeof(sibo_model); }
+
+/* ------------------------------------------------------------------ open-loop latency of the CPU path */
+/*
+ * The reference's shape under load: `threads` executors (INFERENCE_BOLT_PARAL, MainTopology.java:27) each run
+ * execute() on one tuple at a time; tuples arrive on a fixed schedule (tuple i at i/rate seconds) and are dealt to
+ * whichever executor is free next (what shuffle grouping converges to). Latency = completion - scheduled arrival,
+ * so queueing counts; when rate > capacity the latencies grow without bound (reported as is, the run is bounded by
+ * n_tuples). mode 0: JSON in -> JSON out (sibo_execute); mode 1: fp32 image in -> probabilities (model only).
+ */
+#include <time.h>
+static long long now_ns(void) {
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (long long)ts.tv_sec * 1000000000ll + ts.tv_nsec;
+}
+
+typedef struct {
+    const sibo_model *m;
+    const void *const *payloads;
+    const size_t *lens;
+    int n_payloads, mode;
+    double gap_ns;
+    long n_tuples;
+    long long t0;
+    long long *lat;
+    volatile long next;
+} lat_ctx;
+
+static void *lat_worker(void *vp) {
+    lat_ctx *c = (lat_ctx *)vp;
+    float *scratch = (float *)malloc(sizeof(float) * 3 * c->m->max_act);
+    char out[4096];
+    float lg[64], pr[64];
+    for (;;) {
+        long i = __sync_fetch_and_add(&c->next, 1);
+        if (i >= c->n_tuples) break;
+        long long due = c->t0 + (long long)((double)i * c->gap_ns);
+        while (now_ns() < due) { /* spin: arrival not yet due */ }
+        int k = (int)(i % c->n_payloads);
+        if (c->mode == 0) sibo_execute(c->m, (const char *)c->payloads[k], c->lens[k], out, sizeof out);
+        else forward_one_f32(c->m, (const float *)c->payloads[k], lg, pr, scratch);
+        c->lat[i] = now_ns() - due;
+    }
+    free(scratch);
+    return NULL;
+}
+
+int sibo_latency_run(const sibo_model *m, const void *const *payloads, const size_t *lens, int n_payloads, int mode,
+                     double rate_per_s, long n_tuples, int threads, long long *lat_out) {
+    if (threads < 1) threads = sibo_max_threads();
+    if (threads > 256) threads = 256;
+    lat_ctx c;
+    c.m = m; c.payloads = payloads; c.lens = lens; c.n_payloads = n_payloads; c.mode = mode;
+    c.gap_ns = 1e9 / rate_per_s; c.n_tuples = n_tuples; c.lat = lat_out; c.next = 0;
+    c.t0 = now_ns() + 2000000;
+    pthread_t th[256];
+    for (int t = 0; t < threads; t++) pthread_create(&th[t], NULL, lat_worker, &c);
+    for (int t = 0; t < threads; t++) pthread_join(th[t], NULL);
+    return 0;
+}

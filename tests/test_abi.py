@@ -15,7 +15,7 @@ def _declared(header):
 
 def test_every_declared_symbol_is_exported(sib):
     lib = ctypes.CDLL(sib.native.LIB_PATH)
-    names = _declared("sib.h") + _declared("sib_bolt.h")
+    names = _declared("sib.h") + _declared("sib_bolt.h") + _declared("sib_loadgen.h")
     assert len(names) >= 25
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/ but not exported by libsib.so"
@@ -26,6 +26,7 @@ def test_binding_table_covers_header(sib):
     bolt = import_module("sib_b200.bolt")
     assert sorted(sib.native.SYMBOLS) == _declared("sib.h")
     assert sorted(bolt.HARNESS_SYMBOLS) == _declared("sib_bolt.h")
+    assert sorted(sib.native.LOADGEN_SYMBOLS) == [n for n in _declared("sib_loadgen.h") if n.startswith("sib_loadgen")]
 
 
 def test_struct_sizes_match_header(sib):

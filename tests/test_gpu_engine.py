@@ -130,3 +130,23 @@ def test_submit_pinned_is_zero_copy_and_mixes_with_staged(sib, oracle, presets):
         assert np.abs(P - pr).max() <= 1e-5
         st = e.stats()
         assert st.h2d_bytes == 96 * 784 * 4 and st.flush_by_size == 1
+
+
+def test_loadgen_latency_is_bounded_by_deadline_plus_service(sib, presets):
+    """Open-loop arrivals far below capacity: every tuple comes back, and p99 stays near the flush deadline."""
+    m = presets["mnist-lenet5"]
+    ms = sib.modelspec
+    x = ms.synthetic_images(m, 27, 8)
+    payloads = [ms.instances_json(x[i:i + 1]) for i in range(8)]
+    with sib.native.Engine(m.to_blob(), max_batch=256, deadline_us=300) as e:
+        sib.native.loadgen(e, payloads, 2000.0, 500, mode=sib.native.LG_JSON)          # warm-up
+        r = sib.native.loadgen(e, payloads, 5000.0, 5000, mode=sib.native.LG_JSON, producers=2, want_latencies=True)
+        assert r["completed"] == 5000 and r["rejected"] == 0 and r["images"] == 5000
+        lat = r["latencies_ns"]
+        assert (lat > 0).all()
+        assert r["p50_ns"] < 5_000_000 and r["p99_ns"] < 50_000_000                     # ms-scale, generous for a shared box
+        st = e.stats()
+        assert st.flush_by_deadline > 0                                                 # low rate: batches close on the deadline
+    with sib.native.Engine(m.to_blob(), max_batch=64, deadline_us=300) as e:
+        r = sib.native.loadgen(e, [x[i] for i in range(8)], 200000.0, 20000, mode=sib.native.LG_F32, producers=2)
+        assert r["completed"] == 20000
