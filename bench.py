@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--e2e-copy", action="store_true", help="e2e leg through sib_submit_f32 (pageable source, staged copy)")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-latency", action="store_true")
     return ap.parse_args()
 
 
@@ -121,6 +122,62 @@ def cpu_per_tuple(model, seconds: float, threads: int = 0):
         if dt >= seconds:
             break
     return done / dt, cores, f"{done} images of {model.name} (D2 seed 1234), batch 1 per call, {dt:.1f} s wall"
+
+
+def cpu_generous(model, seconds: float):
+    """'Generous' CPU mode: torch-CPU (oneDNN) batched, b=256, all cores, model only. Independent of the oracle's C."""
+    try:
+        import torch
+        import torch_ref
+        import sib_b200 as sib
+        torch.set_num_threads(os.cpu_count() or 8)
+        x = sib.modelspec.synthetic_images(model, 0, 256)
+        blob = model.to_blob()
+        torch_ref.forward(blob, x)
+        done, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < seconds:
+            torch_ref.forward(blob, x, threads=os.cpu_count() or 8)
+            done += 256
+        return done / (time.perf_counter() - t0)
+    except Exception as ex:  # noqa: BLE001
+        return f"unavailable: {ex}"
+
+
+def t2_and_latency(sib, model, blob, prec, guard):
+    """Bolt-level numbers through the C ABI's load generator (include/sib_loadgen.h), N=1 GPU only.
+    T2 saturation: JSON tuples in -> JSON messages out, producers running flat out.
+    Latency: open-loop fixed-interval arrivals; result-available minus scheduled arrival; CPU path beside it."""
+    import oracle
+    native = sib.native
+    ms = sib.modelspec
+    cores = os.cpu_count() or 8
+    prod = max(1, min(8, cores - 2))
+    x = ms.synthetic_images(model, 9, 32)
+    jp = [ms.instances_json(x[i:i + 1]) for i in range(32)]
+    fp = [x[i] for i in range(32)]
+    out = {"producers": prod, "json_bytes_per_tuple": int(np.mean([len(j) for j in jp]))}
+    with native.Engine(blob, max_batch=4096, deadline_us=200, precision=prec, n_slots=6, guard=guard) as e:
+        native.loadgen(e, jp, 20000.0, 2000, mode=native.LG_JSON, producers=prod)
+        r = native.loadgen(e, jp, 5e6, 40000, mode=native.LG_JSON, producers=prod)
+        out["t2_json_tuples_per_s_saturated"] = r["achieved_tuples_per_s"]
+    lat = {}
+    with native.Engine(blob, max_batch=512, deadline_us=200, precision=prec, n_slots=6, guard=guard) as e:
+        native.loadgen(e, jp, 10000.0, 2000, mode=native.LG_JSON, producers=prod)
+        r = native.loadgen(e, jp, 10000.0, 10000, mode=native.LG_JSON, producers=prod)
+        lat["b200_T2_json_10k_per_s"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 200}
+        r = native.loadgen(e, fp, 100000.0, 100000, mode=native.LG_F32, producers=prod)
+        lat["b200_T1_f32_100k_per_s"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 200}
+    with native.Engine(blob, max_batch=64, deadline_us=50, precision=prec, n_slots=6, guard=guard) as e:
+        native.loadgen(e, fp, 10000.0, 2000, mode=native.LG_F32, producers=prod)
+        r = native.loadgen(e, fp, 100000.0, 100000, mode=native.LG_F32, producers=prod)
+        lat["b200_T1_f32_100k_per_s_deadline50"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 50}
+    om = oracle.Model(blob)
+    l = oracle.latency_run(om, jp, 10000.0, 10000, threads=cores, json_mode=True)
+    lat["cpu_T2_json_10k_per_s"] = {"p50_us": float(np.percentile(l, 50)) / 1e3, "p99_us": float(np.percentile(l, 99)) / 1e3, "executors": cores}
+    l = oracle.latency_run(om, fp, 10000.0, 10000, threads=cores, json_mode=False)
+    lat["cpu_T1_f32_10k_per_s"] = {"p50_us": float(np.percentile(l, 50)) / 1e3, "p99_us": float(np.percentile(l, 99)) / 1e3, "executors": cores}
+    out["latency"] = lat
+    return out
 
 
 def run_reference(args):
@@ -372,6 +429,14 @@ def run_ours(args):
     if not args.skip_cpu:
         v, cores, sample = cpu_per_tuple(model, args.cpu_seconds)
         line["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample}
+        # the other CPU shapes BASELINE.md asks for, a few seconds each
+        v1, _, _ = cpu_per_tuple(model, 2.0, threads=1)
+        v4, _, _ = cpu_per_tuple(model, 2.0, threads=4)  # INFERENCE_BOLT_PARAL = 4 (MainTopology.java:27)
+        line["cpu_baseline"]["per_tuple_1_thread"] = v1
+        line["cpu_baseline"]["per_tuple_4_threads"] = v4
+        line["cpu_baseline"]["generous_torch_b256_all_cores"] = cpu_generous(model, 3.0)
+    if not args.skip_latency and world == 1:
+        line["t2_and_latency"] = t2_and_latency(sib, model, blob, prec, not args.no_guard)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

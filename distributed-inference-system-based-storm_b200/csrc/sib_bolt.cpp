@@ -29,6 +29,7 @@ void InferenceBolt::prepare(const Conf& conf, const TopologyContext& ctx, Output
     cfg.deadline_us = conf_int(conf, "sib.deadline.us", 0);
     cfg.n_slots = conf_int(conf, "sib.slots", 0);
     cfg.guard = conf_int(conf, "sib.guard", 1);
+    cfg.json_on_gpu = conf_int(conf, "sib.json.gpu", 0);
     auto tau = conf.find("sib.guard.tau");
     cfg.guard_tau = tau == conf.end() ? 0.0f : (float)std::atof(tau->second.c_str());
     auto pr = conf.find("sib.precision");

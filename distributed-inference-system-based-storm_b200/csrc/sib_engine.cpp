@@ -38,6 +38,14 @@ using Clock = std::chrono::steady_clock;
 struct Entry {
     uint64_t tag;
     int n, offset;
+    int text = -1;        // index into the slot's text-tuple table when the tuple went in as raw JSON
+    int side = -1;        // index into the slot's side results (tuples the host decoder had to redo)
+    int status = SIB_OK;  // per-tuple status (json_on_gpu: SIB_EJSON / SIB_ESHAPE found after the fact)
+};
+
+struct SideResult {
+    std::vector<float> probs;
+    std::vector<int32_t> argmax;
 };
 
 struct DevBufs {  // one forward's worth of device memory
@@ -65,6 +73,16 @@ struct Slot {
     size_t next_entry = 0;
     int images = 0;
     int status = SIB_OK;
+    // raw-JSON tuples (json_on_gpu): text bytes + {offset, length, image index, 0} per tuple, decoded by a kernel
+    char* h_text = nullptr;
+    char* d_text = nullptr;
+    int32_t* h_tdesc = nullptr;
+    int32_t* d_tdesc = nullptr;
+    int32_t* h_tflags = nullptr;
+    int32_t* d_tflags = nullptr;
+    size_t text_cap = 0, text_used = 0;
+    int n_text = 0;
+    std::vector<SideResult> side;
     std::vector<std::pair<int, int>> staged;  // (offset, n) image ranges that sit in h_in and need the H2D at launch
     size_t direct_bytes = 0;                  // bytes already sent device-ward straight from caller-pinned memory
     int writers = 0;       // submitters that reserved room and are copying outside the lock
@@ -102,6 +120,7 @@ struct sib_engine {
     void free_slot(Slot& s);
     int run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax, GuardScratch* g,
                     cudaStream_t st);
+    void redo_flagged_locked(Slot& s);    // json_on_gpu: tuples the decode kernel declined go through the host decoder
     int seal_locked(int si, int reason);  // stop filling; launches at once unless a writer is still copying
     int launch_locked(int si);
     void deadline_main();
@@ -139,6 +158,17 @@ int sib_engine::alloc_slot(Slot& s) {
     s.h_guard_n[0] = 0;
     int r = alloc_dev(s.dev, true);
     if (r) return r;
+    if (cfg.json_on_gpu) {
+        // room for ~14 characters per pixel value; a slot also seals when its text area is full
+        const size_t per_img = std::min<size_t>(json_gpu_max_text(), 16 + 14 * (size_t)model.img_elems);
+        s.text_cap = std::min<size_t>(mb, 8192) * per_img + 64;
+        CU_TRY(cudaHostAlloc((void**)&s.h_text, s.text_cap, cudaHostAllocDefault));
+        CU_TRY(cudaMalloc((void**)&s.d_text, s.text_cap));
+        CU_TRY(cudaHostAlloc((void**)&s.h_tdesc, mb * 4 * sizeof(int32_t), cudaHostAllocDefault));
+        CU_TRY(cudaMalloc((void**)&s.d_tdesc, mb * 4 * sizeof(int32_t)));
+        CU_TRY(cudaHostAlloc((void**)&s.h_tflags, mb * sizeof(int32_t), cudaHostAllocDefault));
+        CU_TRY(cudaMalloc((void**)&s.d_tflags, mb * sizeof(int32_t)));
+    }
     CU_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
     s.entries.reserve(256);
@@ -148,6 +178,8 @@ int sib_engine::alloc_slot(Slot& s) {
 void sib_engine::free_slot(Slot& s) {
     if (s.stream) cudaStreamSynchronize(s.stream);
     cudaFreeHost(s.h_in); cudaFreeHost(s.h_probs); cudaFreeHost(s.h_argmax); cudaFreeHost(s.h_guard_n);
+    cudaFreeHost(s.h_text); cudaFreeHost(s.h_tdesc); cudaFreeHost(s.h_tflags);
+    cudaFree(s.d_text); cudaFree(s.d_tdesc); cudaFree(s.d_tflags);
     free_dev(s.dev);
     if (s.done) cudaEventDestroy(s.done);
     if (s.stream) cudaStreamDestroy(s.stream);
@@ -208,6 +240,17 @@ int sib_engine::launch_locked(int si) {
                             (size_t)r.second * img_bytes, cudaMemcpyHostToDevice, s.stream), "H2D");
         in_bytes += (size_t)r.second * img_bytes;
     }
+    if (s.n_text > 0) {  // raw JSON tuples: ship the text, decode it on the device into d_in
+        chk(cudaMemcpyAsync(s.d_text, s.h_text, s.text_used + 16, cudaMemcpyHostToDevice, s.stream), "H2D text");
+        chk(cudaMemcpyAsync(s.d_tdesc, s.h_tdesc, (size_t)s.n_text * 4 * sizeof(int32_t), cudaMemcpyHostToDevice, s.stream), "H2D text table");
+        in_bytes += s.text_used + (size_t)s.n_text * 16;
+        if (rc == SIB_OK) {
+            int ke = launch_json_decode(s.d_text, s.d_tdesc, s.n_text, s.dev.d_in, s.d_tflags, (int)model.in_h, (int)model.in_w, (int)model.in_c, s.stream);
+            stats.kernel_launches += 1;
+            if (ke) { set_error(std::string("json decode kernel: ") + cudaGetErrorString((cudaError_t)ke)); rc = SIB_ECUDA; }
+        }
+        chk(cudaMemcpyAsync(s.h_tflags, s.d_tflags, (size_t)s.n_text * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H text flags");
+    }
     if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
     chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)s.images * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream), "D2H probs");
     chk(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)s.images * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H argmax");
@@ -230,6 +273,37 @@ int sib_engine::launch_locked(int si) {
     stats.batch_hist[b]++;
     cv.notify_all();
     return rc;
+}
+
+extern "C" int sib_forward_sync(sib_engine* e, const float* x, int n, float* probs, float* logits, int32_t* argmax);
+
+// The decode kernel only takes one-instance tuples in canonical form; whatever it flagged is read again here with
+// the host decoder, which owns the complete Jackson semantics (leniencies, N > 1, error classes). Rare path.
+void sib_engine::redo_flagged_locked(Slot& s) {
+    const size_t nc = model.n_classes;
+    std::vector<float> tmp;
+    for (auto& en : s.entries) {
+        if (en.text < 0 || !s.h_tflags[en.text]) continue;
+        const char* txt = s.h_text + s.h_tdesc[4 * en.text];
+        const size_t len = (size_t)s.h_tdesc[4 * en.text + 1];
+        const long cap = (long)(len / 2 + 8);
+        if ((long)tmp.size() < cap) tmp.resize((size_t)cap);
+        int64_t dims[4] = {0, 0, 0, 0};
+        const long nf = json_decode(txt, len, tmp.data(), cap, dims);
+        if (nf == SIB_EJSON) { en.n = 0; en.status = SIB_EJSON; continue; }
+        if (nf < 0 || dims[1] != model.in_h || dims[2] != model.in_w || dims[3] != model.in_c || dims[0] > cfg.max_batch) {
+            en.n = 0; en.status = SIB_ESHAPE; continue;
+        }
+        SideResult sr;
+        sr.probs.resize((size_t)dims[0] * nc);
+        sr.argmax.resize((size_t)dims[0]);
+        if (sib_forward_sync(this, tmp.data(), (int)dims[0], sr.probs.data(), nullptr, sr.argmax.data()) != SIB_OK) {
+            en.n = 0; en.status = SIB_ECUDA; continue;
+        }
+        en.n = (int)dims[0];
+        en.side = (int)s.side.size();
+        s.side.push_back(std::move(sr));
+    }
 }
 
 void sib_engine::deadline_main() {
@@ -285,6 +359,7 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     if (c.max_batch <= 0) c.max_batch = 4096;
     if (c.deadline_us <= 0) c.deadline_us = 200;
     if (c.n_slots < 2) c.n_slots = 4;
+    c.json_on_gpu = c.json_on_gpu ? 1 : 0;
     if (c.precision != SIB_PREC_FP16 && c.precision != SIB_PREC_BF16 && c.precision != SIB_PREC_FP32) {
         set_error("precision must be SIB_PREC_FP16, SIB_PREC_BF16 or SIB_PREC_FP32");
         delete e;
@@ -384,6 +459,9 @@ static int slot_for(sib_engine* e, int n) {
                 s.state = Slot::FILLING;
                 s.staged.clear();
                 s.direct_bytes = 0;
+                s.text_used = 0;
+                s.n_text = 0;
+                s.side.clear();
                 s.writers = 0;
                 s.images = 0;
                 s.entries.clear();
@@ -471,6 +549,38 @@ extern "C" int sib_submit_json(sib_engine* e, uint64_t tag, const char* utf8, si
     if (!e || !utf8) return SIB_EINVAL;
     const ModelDesc& m = e->model;
     const size_t img = m.img_elems;
+    if (e->cfg.json_on_gpu && len >= 16 && len <= json_gpu_max_text()) {
+        // Raw path: the text itself goes into the slot's pinned text area and is decoded by a kernel after the H2D.
+        // The engine learns only at completion whether the tuple was well-formed (sib_result.status).
+        Slot* s;
+        int si;
+        size_t toff;
+        {
+            std::unique_lock<std::mutex> lk(e->mu);
+            if (e->closing) return SIB_ECLOSED;
+            si = slot_for(e, 1);
+            if (si < 0) return si;
+            s = &e->slots[si];
+            toff = (s->text_used + 15) & ~(size_t)15;
+            if (toff + len + 32 > s->text_cap) {  // text area full before the image count: close this batch
+                e->seal_locked(si, 0);
+                si = slot_for(e, 1);
+                if (si < 0) return si;
+                s = &e->slots[si];
+                toff = 0;
+            }
+            const int off = reserve(e, si, tag, 1, false);
+            int32_t* d = s->h_tdesc + 4 * s->n_text;
+            d[0] = (int32_t)toff; d[1] = (int32_t)len; d[2] = off; d[3] = 0;
+            for (auto it = s->entries.rbegin(); it != s->entries.rend(); ++it)
+                if (it->offset == off) { it->text = s->n_text; break; }
+            s->n_text++;
+            s->text_used = toff + len;
+        }
+        std::memcpy(s->h_text + toff, utf8, len);
+        written(e, si);
+        return 1;
+    }
     // The usual tuple carries one instance (InferenceBolt.java:86 hard-wires [1][10]): reserve one image and decode
     // the text straight into the pinned slot, outside the lock. A tuple with more instances does not fit that
     // reservation; it is decoded into a thread-local buffer and copied in like sib_submit_f32 does.
@@ -554,14 +664,16 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                 }
                 s.state = Slot::READY;
                 if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.h_guard_n[0];
+                if (s.n_text > 0) e->redo_flagged_locked(s);
             }
             while (got < max && s.next_entry < s.entries.size()) {
                 const Entry& en = s.entries[s.next_entry++];
-                if (en.n == 0) continue;  // reservation that was given back (see sib_submit_json)
+                if (en.n == 0 && en.status == SIB_OK) continue;  // reservation that was given back (see sib_submit_json)
                 sib_result& r = out[got++];
-                r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status; r.reserved = 0;
-                r.probs = s.h_probs + (size_t)en.offset * nc;
-                r.argmax = s.h_argmax + en.offset;
+                r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status != SIB_OK ? s.status : en.status; r.reserved = 0;
+                if (en.n == 0) { r.probs = nullptr; r.argmax = nullptr; }
+                else if (en.side >= 0) { r.probs = s.side[(size_t)en.side].probs.data(); r.argmax = s.side[(size_t)en.side].argmax.data(); }
+                else { r.probs = s.h_probs + (size_t)en.offset * nc; r.argmax = s.h_argmax + en.offset; }
             }
             if (s.next_entry == s.entries.size()) {
                 s.state = Slot::HANDED;

@@ -74,6 +74,11 @@ size_t tc_debug_floats(int preset);
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
                       GuardScratch* guard, float tau, float* d_dbg, void* stream);
 
+// GPU-side JSON decode (sib_kernels_json.cu): one CTA per tuple; desc = {text offset, length, image index, 0} x n.
+size_t json_gpu_max_text();
+int launch_json_decode(const char* d_text, const int32_t* d_desc, int n_tuples, float* d_out, int32_t* d_flags, int H,
+                       int W, int C, void* stream);
+
 // Read-only view of an open engine for translation units that add entry points next to sib_engine.cpp.
 struct EngineView {
     int device = 0, precision = 0, guard = 0, preset = -1;

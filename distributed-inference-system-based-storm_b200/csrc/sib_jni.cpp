@@ -18,7 +18,7 @@ JNIEXPORT jlong JNICALL Java_dke_model_NativeInfer_open(JNIEnv* env, jclass, jby
     env->GetByteArrayRegion(blob, 0, n, b.data());
     jint c[7] = {-1, 0, 0, 0, 0, 0, 1};
     env->GetIntArrayRegion(cfg, 0, 7, c);
-    sib_config sc{c[0], c[1], c[2], c[3], c[4], c[5], c[6], tau};
+    sib_config sc{c[0], c[1], c[2], c[3], c[4], c[5], c[6], tau, 0};
     sib_engine* e = nullptr;
     if (sib_engine_open(b.data(), (size_t)n, &sc, &e) != SIB_OK) return 0;
     return (jlong)(intptr_t)e;

@@ -24,7 +24,7 @@ lib = C.CDLL(LIB_PATH)
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("task_index", C.c_int32), ("max_batch", C.c_int32),
                 ("deadline_us", C.c_int32), ("precision", C.c_int32), ("n_slots", C.c_int32),
-                ("guard", C.c_int32), ("guard_tau", C.c_float)]
+                ("guard", C.c_int32), ("guard_tau", C.c_float), ("json_on_gpu", C.c_int32)]
 
 
 class Result(C.Structure):
@@ -136,10 +136,11 @@ class Engine:
 
     def __init__(self, blob: bytes, device: int = -1, task_index: int = 0, max_batch: int = 4096,
                  deadline_us: int = 200, precision: int = PREC_FP16, n_slots: int = 4, guard: bool = True,
-                 guard_tau: float = 0.0):
+                 guard_tau: float = 0.0, json_on_gpu: bool = False):
         self._h = C.c_void_p()
         self._blob = blob
-        cfg = Config(device, task_index, max_batch, deadline_us, precision, n_slots, 1 if guard else 0, guard_tau)
+        cfg = Config(device, task_index, max_batch, deadline_us, precision, n_slots, 1 if guard else 0, guard_tau,
+                     1 if json_on_gpu else 0)
         rc = lib.sib_engine_open(blob, len(blob), C.byref(cfg), C.byref(self._h))
         if rc:
             raise SibError(rc, "sib_engine_open")
@@ -200,6 +201,9 @@ class Engine:
         out = []
         for i in range(n):
             r = res[i]
+            if r.n == 0 or not r.probs:
+                out.append((int(r.tag), None, None, int(r.status)))
+                continue
             pr = np.ctypeslib.as_array(r.probs, (r.n, r.n_classes)).copy()
             am = np.ctypeslib.as_array(r.argmax, (r.n,)).copy()
             out.append((int(r.tag), pr, am, int(r.status)))
@@ -211,6 +215,9 @@ class Engine:
         out = []
         buf = C.create_string_buffer(1 << 16)
         for i in range(n):
+            if res[i].status != OK or res[i].n == 0:
+                out.append((int(res[i].tag), None))   # the bolt emits a null message for these
+                continue
             need = 64 + res[i].n * (res[i].n_classes * 18 + 4)
             if need > len(buf):
                 buf = C.create_string_buffer(need)

@@ -52,6 +52,11 @@ typedef struct sib_config {
     int32_t n_slots;     /* pinned batch slots in the ring, >= 2               (default 4)    */
     int32_t guard;       /* 1 = recompute low-margin images in fp32 so argmax equals the fp32 path (default 1) */
     float guard_tau;     /* top1-top2 logit margin below which the guard recomputes (default 0.05 FP16, 0.30 BF16) */
+    int32_t json_on_gpu; /* 1 = sib_submit_json ships the raw UTF-8 to the GPU and a CUDA kernel decodes it (one
+                            instance per tuple, canonical nesting); tuples it cannot take are re-read by the host
+                            decoder when their batch completes, so results are the same either way. In this mode a
+                            malformed or wrong-shaped tuple is reported in sib_result.status (SIB_EJSON / SIB_ESHAPE,
+                            n = 0) instead of by sib_submit_json's return value. (default 0) */
 } sib_config;
 
 /* One completed tuple. probs/argmax are engine-owned and stay valid until the next sib_poll() on the engine. */
@@ -59,7 +64,7 @@ typedef struct sib_result {
     uint64_t tag;          /* caller's tuple handle, returned untouched */
     int32_t n;             /* images in the tuple (rows of predictions) */
     int32_t n_classes;     /* columns of predictions (10 for the reference: InferenceBolt.java:86) */
-    int32_t status;        /* SIB_OK or SIB_ECUDA */
+    int32_t status;        /* SIB_OK, SIB_ECUDA, or (json_on_gpu) SIB_EJSON / SIB_ESHAPE with n = 0 and probs = NULL */
     int32_t reserved;
     const float *probs;    /* n x n_classes softmax probabilities, "output/Softmax:0" (InferenceBolt.java:83) */
     const int32_t *argmax; /* n predicted classes (first maximum) */

@@ -21,10 +21,10 @@ def parse_blob(blob: bytes):
     return (h, w, c), layers, wt
 
 
-def forward(blob: bytes, x: np.ndarray, dtype=torch.float32):
+def forward(blob: bytes, x: np.ndarray, dtype=torch.float32, threads: int = 1):
     """x [N,H,W,C] -> (logits, probs) as numpy arrays of `dtype`."""
     (h, w, c), layers, wt = parse_blob(blob)
-    torch.set_num_threads(1)
+    torch.set_num_threads(threads)
     t = torch.from_numpy(np.ascontiguousarray(x, np.float32)).to(dtype).permute(0, 3, 1, 2)  # NCHW
     flat = None
     for kind, a, b, cin, cout, flags, w_off, b_off in layers:
