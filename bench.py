@@ -159,7 +159,11 @@ def t2_and_latency(sib, model, blob, prec, guard):
     with native.Engine(blob, max_batch=4096, deadline_us=200, precision=prec, n_slots=6, guard=guard) as e:
         native.loadgen(e, jp, 20000.0, 2000, mode=native.LG_JSON, producers=prod)
         r = native.loadgen(e, jp, 5e6, 40000, mode=native.LG_JSON, producers=prod)
-        out["t2_json_tuples_per_s_saturated"] = r["achieved_tuples_per_s"]
+        out["t2_json_tuples_per_s_saturated_host_decode"] = r["achieved_tuples_per_s"]
+    with native.Engine(blob, max_batch=4096, deadline_us=200, precision=prec, n_slots=6, guard=guard, json_on_gpu=True) as e:
+        native.loadgen(e, jp, 20000.0, 2000, mode=native.LG_JSON, producers=prod)
+        r = native.loadgen(e, jp, 5e6, 200000, mode=native.LG_JSON, producers=prod)
+        out["t2_json_tuples_per_s_saturated_gpu_decode"] = r["achieved_tuples_per_s"]
     lat = {}
     with native.Engine(blob, max_batch=512, deadline_us=200, precision=prec, n_slots=6, guard=guard) as e:
         native.loadgen(e, jp, 10000.0, 2000, mode=native.LG_JSON, producers=prod)
@@ -167,6 +171,11 @@ def t2_and_latency(sib, model, blob, prec, guard):
         lat["b200_T2_json_10k_per_s"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 200}
         r = native.loadgen(e, fp, 100000.0, 100000, mode=native.LG_F32, producers=prod)
         lat["b200_T1_f32_100k_per_s"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 200}
+    with native.Engine(blob, max_batch=512, deadline_us=200, precision=prec, n_slots=6, guard=guard, json_on_gpu=True) as e:
+        native.loadgen(e, jp, 10000.0, 2000, mode=native.LG_JSON, producers=prod)
+        r = native.loadgen(e, jp, 100000.0, 100000, mode=native.LG_JSON, producers=prod)
+        lat["b200_T2_json_100k_per_s_gpu_decode"] = {"p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3, "deadline_us": 200,
+                                                     "late_submits": r["late_submits"]}
     with native.Engine(blob, max_batch=64, deadline_us=50, precision=prec, n_slots=6, guard=guard) as e:
         native.loadgen(e, fp, 10000.0, 2000, mode=native.LG_F32, producers=prod)
         r = native.loadgen(e, fp, 100000.0, 100000, mode=native.LG_F32, producers=prod)
