@@ -283,7 +283,9 @@ void sib_engine::redo_flagged_locked(Slot& s) {
     const size_t nc = model.n_classes;
     std::vector<float> tmp;
     for (auto& en : s.entries) {
-        if (en.text < 0 || !s.h_tflags[en.text]) continue;
+        if (en.text < 0) continue;
+        if (!s.h_tflags[en.text]) { stats.json_gpu_decoded++; continue; }
+        stats.json_host_redone++;
         const char* txt = s.h_text + s.h_tdesc[4 * en.text];
         const size_t len = (size_t)s.h_tdesc[4 * en.text + 1];
         const long cap = (long)(len / 2 + 8);

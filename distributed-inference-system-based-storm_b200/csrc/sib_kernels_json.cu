@@ -34,6 +34,11 @@ __device__ __forceinline__ bool is_digit(unsigned char c) { return (unsigned)(c 
 __device__ __forceinline__ bool is_num(unsigned char c) {
     return is_digit(c) || c == '-' || c == '+' || c == '.' || c == 'e' || c == 'E';
 }
+// A number token starts at a digit or '-' that does not continue a number ('e' alone is not a start: the key
+// "instances" contains one).
+__device__ __forceinline__ bool is_start(const unsigned char* s, int i) {
+    return (is_digit(s[i]) || s[i] == '-') && !(i > 0 && is_num(s[i - 1]));
+}
 
 // walks backwards over optional whitespace and expects `ch`; returns false if something else is there
 __device__ __forceinline__ bool back_expect(const unsigned char* s, int& q, unsigned char ch) {
@@ -76,9 +81,7 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
     const int lo = tid * chunk, hi = min(len, lo + chunk);
     int cnt = 0;
     for (int i = lo; i < hi; i++) {
-        const bool cur = is_num(s[i]);
-        const bool prev = i > 0 && is_num(s[i - 1]);
-        cnt += (cur && !prev) ? 1 : 0;
+        cnt += is_start(s, i) ? 1 : 0;
     }
     s_cnt[tid] = cnt;
     __syncthreads();
@@ -110,7 +113,7 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
     bool bad = false;
     float* dst = out + (size_t)img * elems;
     for (int i = lo; i < hi; i++) {
-        if (!is_num(s[i]) || (i > 0 && is_num(s[i - 1]))) continue;
+        if (!is_start(s, i)) continue;
         // -- number, RFC 8259 grammar
         int p = i;
         bool neg = false;

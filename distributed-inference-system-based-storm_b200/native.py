@@ -36,7 +36,8 @@ class Stats(C.Structure):
     _fields_ = [("tuples", C.c_uint64), ("images", C.c_uint64), ("batches", C.c_uint64),
                 ("flush_by_size", C.c_uint64), ("flush_by_deadline", C.c_uint64), ("flush_explicit", C.c_uint64),
                 ("guard_recomputed", C.c_uint64), ("batch_hist", C.c_uint64 * 16),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("kernel_launches", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("json_gpu_decoded", C.c_uint64), ("json_host_redone", C.c_uint64)]
 
 
 class ModelInfo(C.Structure):

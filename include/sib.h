@@ -77,6 +77,8 @@ typedef struct sib_stats {
     uint64_t batch_hist[16];   /* batch sizes, bucket b counts batches with 2^b <= images < 2^(b+1) */
     uint64_t h2d_bytes, d2h_bytes;
     uint64_t kernel_launches;
+    uint64_t json_gpu_decoded; /* json_on_gpu: tuples the decode kernel took */
+    uint64_t json_host_redone; /* json_on_gpu: tuples it declined, re-read by the host decoder at completion */
 } sib_stats;
 
 typedef struct sib_model_info {

@@ -34,7 +34,7 @@ def test_struct_sizes_match_header(sib):
     assert ctypes.sizeof(n.Config) == 36
     assert ctypes.sizeof(n.Result) == 40
     assert ctypes.sizeof(n.ModelInfo) == 40
-    assert ctypes.sizeof(n.Stats) == 8 * (7 + 16 + 3)
+    assert ctypes.sizeof(n.Stats) == 8 * (7 + 16 + 5)
 
 
 def test_model_describe_and_errors_without_gpu(sib, presets):

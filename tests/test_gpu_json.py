@@ -68,6 +68,8 @@ def test_gpu_decode_is_bit_exact_with_host_decode(sib, presets):
         assert p.tobytes() == ref[i:i + 1].tobytes(), f"tuple {i}: decoded input differs from Jackson's text->double->float"
         assert a[0] == ref_am[i]
     assert st.tuples == 48 and st.images == 48
+    # the kernel itself took the tuples it is meant for; only the 17-digit style (1 in 6) went to the host decoder
+    assert st.json_gpu_decoded >= 38 and st.json_gpu_decoded + st.json_host_redone == 48
 
 
 def test_gpu_decode_hands_the_unusual_to_the_host_decoder(sib, oracle, presets):
@@ -135,4 +137,4 @@ def test_gpu_decode_full_rate(sib, presets):
         r = sib.native.loadgen(e, payloads, 50000.0, 20000, mode=sib.native.LG_JSON, producers=2)
         assert r["completed"] == 20000 and r["rejected"] == 0
         st = e.stats()
-        assert st.images == 20000
+        assert st.images == 20000 and st.json_gpu_decoded == 20000 and st.json_host_redone == 0
