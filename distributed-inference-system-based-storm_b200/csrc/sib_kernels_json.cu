@@ -24,7 +24,8 @@ namespace sib {
 namespace {
 
 constexpr int kJT = 256;
-constexpr int kMaxText = 60 * 1024;  // bytes of one tuple staged in shared memory; longer tuples go to the host
+constexpr int kMaxText = 56 * 1024;  // bytes of one tuple staged in shared memory; longer tuples go to the host
+constexpr int kMaxElems = 4096;      // token positions kept behind the text (2 bytes each)
 
 __constant__ double c_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
@@ -65,7 +66,7 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
     const int off = desc[4 * t], len = desc[4 * t + 1], img = desc[4 * t + 2];
     const int elems = H * W * Cc;
     if (tid == 0) s_bad = 0;
-    if (len > kMaxText || len < 16) {
+    if (len > kMaxText || len < 16 || elems > kMaxElems) {
         if (tid == 0) flags[t] = 1;
         return;
     }
@@ -108,12 +109,21 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
         if (tid == 0) flags[t] = 1;
         return;
     }
-    // ---- pass B: parse each token, check the punctuation in front of it, store
-    int k = s_cnt[tid];
+    // ---- pass B: record where every token starts (thread-sequential over its chunk, but cheap) ...
+    unsigned short* pos = reinterpret_cast<unsigned short*>(s + ((len + 15) & ~15));  // elems x 2 bytes behind the text
+    {
+        int k = s_cnt[tid];
+        for (int i = lo; i < hi; i++)
+            if (is_start(s, i)) pos[k++] = (unsigned short)i;
+    }
+    __syncthreads();
+    // ---- ... pass C: one token per lane at a time, so a warp parses 32 numbers in lock-step instead of taking the
+    // parse body once per byte position (the byte-driven form ran 10x longer: every position starts a token in
+    // SOME lane). Parse, check the punctuation in front of it, store.
     bool bad = false;
     float* dst = out + (size_t)img * elems;
-    for (int i = lo; i < hi; i++) {
-        if (!is_start(s, i)) continue;
+    for (int k = tid; k < elems; k += kJT) {
+        const int i = pos[k];
         // -- number, RFC 8259 grammar
         int p = i;
         bool neg = false;
@@ -186,7 +196,6 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
                       fwd_expect(s, len, f, ']') && fwd_expect(s, len, f, '}');
             bad |= !ok;
         }
-        k++;
     }
     if (bad) s_bad = 1;
     __syncthreads();
@@ -204,11 +213,11 @@ int launch_json_decode(const char* d_text, const int32_t* d_desc, int n_tuples, 
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(json_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxText + 16);
+        cudaError_t e = cudaFuncSetAttribute(json_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxText + 16 + 2 * kMaxElems);
         if (e != cudaSuccess) return (int)e;
         configured[dev & 63] = true;
     }
-    json_decode_kernel<<<n_tuples, kJT, kMaxText + 16, (cudaStream_t)stream>>>(
+    json_decode_kernel<<<n_tuples, kJT, kMaxText + 16 + 2 * kMaxElems, (cudaStream_t)stream>>>(
         reinterpret_cast<const unsigned char*>(d_text), d_desc, d_out, d_flags, H, W, C);
     return (int)cudaGetLastError();
 }
