@@ -1,4 +1,4 @@
-// sib_kernels_guard.cu -- the margin guard's recompute path: fp32 CUDA-core LeNet-5 forward, one image per CTA.
+// sib_kernels_guard.cu -- the margin guard's recompute path: fp32 CUDA-core LeNet-5 forward, up to four listed images per CTA pass.
 //
 // The tensor-core kernel lists the images whose top1-top2 logit margin is below tau (sib_kernels_tc.cu); this
 // kernel re-runs exactly those images in fp32 and overwrites their outputs, so that the emitted argmax equals the
@@ -14,6 +14,8 @@ namespace sib {
 namespace {
 
 constexpr int kGT = 256;
+constexpr int kGI = 4;  // images per CTA pass: the dense weights stream from L2 once per 4 images, and the conv
+                        // stages have 4x the work items to spread over the 256 threads
 
 template <int H_, int W_, int C_>
 struct GNet {
@@ -23,19 +25,19 @@ struct GNet {
     static constexpr int IMG = H * W * C, P1 = PH1 * PW1 * C1, FEAT = PH2 * PW2 * C2;
     static constexpr int NW1 = 25 * C * C1, NW2 = 25 * C1 * C2;
     static constexpr int KSL = 8;  // k slices of fc1
-    static_assert(PH1 * PW1 <= kGT && PH2 * PW2 * 4 <= kGT && FEAT % KSL == 0 && IMG % 4 == 0, "mapping");
+    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && 3 * F2 <= kGT && kGI * 32 <= kGT, "mapping");
     // shared memory (floats)
-    static constexpr int S_IMG = 0, S_W1 = S_IMG + IMG, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
-                         S_W2 = S_P1 + P1, S_P2 = S_W2 + NW2 + C2, S_PART = S_P2 + FEAT, S_H1 = S_PART + KSL * F1,
-                         S_H2 = S_H1 + F1, S_LG = S_H2 + 3 * F2, S_TOTAL = S_LG + 16;
+    static constexpr int S_IMG = 0, S_W1 = S_IMG + kGI * IMG, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
+                         S_W2 = S_P1 + kGI * P1, S_P2 = S_W2 + NW2 + C2, S_PART = S_P2 + kGI * FEAT,
+                         S_H1 = S_PART + kGI * KSL * F1, S_H2 = S_H1 + kGI * F1, S_TOTAL = S_H2 + kGI * 3 * F2;
 };
 
 template <typename G>
 __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const float* __restrict__ in,
-                                                        const int32_t* __restrict__ list,
-                                                        const int32_t* __restrict__ count, int cap,
-                                                        float* __restrict__ probs, float* __restrict__ logits,
-                                                        int32_t* __restrict__ argmax) {
+                                                           const int32_t* __restrict__ list,
+                                                           const int32_t* __restrict__ count, int cap,
+                                                           float* __restrict__ probs, float* __restrict__ logits,
+                                                           int32_t* __restrict__ argmax) {
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x;
     const int n = min(*count, cap);
@@ -47,18 +49,20 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
     for (int i = tid; i < G::NW2; i += kGT) sm[G::S_W2 + i] = __ldg(W + L1.w_off + i);
     for (int i = tid; i < G::C2; i += kGT) sm[G::S_W2 + G::NW2 + i] = __ldg(W + L1.b_off + i);
 
-    for (int it = blockIdx.x; it < n; it += gridDim.x) {
-        const int img = list[it];
+    for (int it = blockIdx.x * kGI; it < n; it += gridDim.x * kGI) {
+        const int imgs = min(kGI, n - it);
         __syncthreads();
-        {
+        for (int g = 0; g < kGI; g++) {  // rows past the end of the list repeat the last image (results dropped)
+            const int img = list[it + min(g, imgs - 1)];
             const float4* s4 = reinterpret_cast<const float4*>(in + (size_t)img * G::IMG);
-            float4* d4 = reinterpret_cast<float4*>(sm + G::S_IMG);
+            float4* d4 = reinterpret_cast<float4*>(sm + G::S_IMG + g * G::IMG);
             for (int i = tid; i < G::IMG / 4; i += kGT) d4[i] = __ldg(s4 + i);
         }
         __syncthreads();
-        // ---- conv1 + bias + ReLU + pool: one thread per pooled position, 2x2 positions x 6 channels in registers
-        if (tid < G::PH1 * G::PW1) {
-            const int py = tid / G::PW1, px = tid % G::PW1;
+        // ---- conv1 + bias + ReLU + pool: item = (image, pooled position); 2x2 positions x 6 channels in registers
+        for (int item = tid; item < kGI * G::PH1 * G::PW1; item += kGT) {
+            const int g = item / (G::PH1 * G::PW1), pp = item % (G::PH1 * G::PW1);
+            const int py = pp / G::PW1, px = pp % G::PW1;
             float acc[2][2][G::C1];
 #pragma unroll
             for (int a = 0; a < 2; a++)
@@ -66,8 +70,8 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
                 for (int b = 0; b < 2; b++)
 #pragma unroll
                     for (int c = 0; c < G::C1; c++) acc[a][b][c] = 0.f;
-            const float* ip = sm + G::S_IMG + ((2 * py) * G::W + 2 * px) * G::C;
-#pragma unroll
+            const float* ip = sm + G::S_IMG + g * G::IMG + ((2 * py) * G::W + 2 * px) * G::C;
+#pragma unroll 1
             for (int r = 0; r < 6; r++) {  // patch row r feeds output row dy with kernel row r-dy
                 float row[6 * G::C];
 #pragma unroll
@@ -93,13 +97,14 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 #pragma unroll
             for (int co = 0; co < G::C1; co++) {
                 const float mx = fmaxf(fmaxf(acc[0][0][co], acc[0][1][co]), fmaxf(acc[1][0][co], acc[1][1][co]));
-                sm[G::S_P1 + (py * G::PW1 + px) * G::C1 + co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + co], 0.f);
+                sm[G::S_P1 + g * G::P1 + pp * G::C1 + co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + co], 0.f);
             }
         }
         __syncthreads();
-        // ---- conv2 + bias + ReLU + pool: thread = (pooled position, 4 output channels)
-        if (tid < G::PH2 * G::PW2 * 4) {
-            const int q = tid & 3, pos = tid >> 2;
+        // ---- conv2 + bias + ReLU + pool: item = (image, pooled position, 4 output channels)
+        for (int item = tid; item < kGI * G::PH2 * G::PW2 * 4; item += kGT) {
+            const int q = item & 3, t2 = item >> 2;
+            const int g = t2 / (G::PH2 * G::PW2), pos = t2 % (G::PH2 * G::PW2);
             const int py = pos / G::PW2, px = pos % G::PW2;
             float acc[2][2][4];
 #pragma unroll
@@ -108,8 +113,8 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
                 for (int b = 0; b < 2; b++)
 #pragma unroll
                     for (int c = 0; c < 4; c++) acc[a][b][c] = 0.f;
-            const float* ip = sm + G::S_P1 + ((2 * py) * G::PW1 + 2 * px) * G::C1;
-#pragma unroll
+            const float* ip = sm + G::S_P1 + g * G::P1 + ((2 * py) * G::PW1 + 2 * px) * G::C1;
+#pragma unroll 1
             for (int r = 0; r < 6; r++) {
                 float row[6 * G::C1];
 #pragma unroll
@@ -134,75 +139,95 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 #pragma unroll
             for (int c = 0; c < 4; c++) {
                 const float mx = fmaxf(fmaxf(acc[0][0][c], acc[0][1][c]), fmaxf(acc[1][0][c], acc[1][1][c]));
-                sm[G::S_P2 + pos * G::C2 + 4 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 4 * q + c], 0.f);  // (h,w,c) flatten
+                sm[G::S_P2 + g * G::FEAT + pos * G::C2 + 4 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 4 * q + c], 0.f);  // (h,w,c) flatten
             }
         }
         __syncthreads();
-        // ---- fc1: 8 k-slices x 30 float4 columns, weights streamed from L2 with 128-bit loads
+        // ---- fc1: 8 k-slices x 30 float4 columns; each 128-bit weight load from L2 serves the 4 images
         if (tid < G::KSL * (G::F1 / 4)) {
             const int n4 = tid % (G::F1 / 4), ks = tid / (G::F1 / 4);
             constexpr int KL = G::FEAT / G::KSL;
             const float4* wp = reinterpret_cast<const float4*>(W + L2.w_off) + (size_t)(ks * KL) * (G::F1 / 4) + n4;
             const float* xp = sm + G::S_P2 + ks * KL;
-            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 10
+            float4 a[kGI];
+#pragma unroll
+            for (int g = 0; g < kGI; g++) a[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 5
             for (int k = 0; k < KL; k++) {
                 const float4 w = __ldg(wp + (size_t)k * (G::F1 / 4));
-                const float x = xp[k];
-                a.x = fmaf(x, w.x, a.x); a.y = fmaf(x, w.y, a.y); a.z = fmaf(x, w.z, a.z); a.w = fmaf(x, w.w, a.w);
-            }
-            *reinterpret_cast<float4*>(sm + G::S_PART + ks * G::F1 + 4 * n4) = a;
-        }
-        __syncthreads();
-        if (tid < G::F1) {
-            float v = __ldg(W + L2.b_off + tid);
 #pragma unroll
-            for (int ks = 0; ks < G::KSL; ks++) v += sm[G::S_PART + ks * G::F1 + tid];
-            sm[G::S_H1 + tid] = fmaxf(v, 0.f);
+                for (int g = 0; g < kGI; g++) {
+                    const float x = xp[g * G::FEAT + k];
+                    a[g].x = fmaf(x, w.x, a[g].x); a[g].y = fmaf(x, w.y, a[g].y);
+                    a[g].z = fmaf(x, w.z, a[g].z); a[g].w = fmaf(x, w.w, a[g].w);
+                }
+            }
+#pragma unroll
+            for (int g = 0; g < kGI; g++)
+                *reinterpret_cast<float4*>(sm + G::S_PART + (g * G::KSL + ks) * G::F1 + 4 * n4) = a[g];
         }
         __syncthreads();
-        // ---- fc2: 3 k-slices x 84 outputs
+        for (int o = tid; o < kGI * G::F1; o += kGT) {
+            const int g = o / G::F1, j = o % G::F1;
+            float v = __ldg(W + L2.b_off + j);
+#pragma unroll
+            for (int ks = 0; ks < G::KSL; ks++) v += sm[G::S_PART + (g * G::KSL + ks) * G::F1 + j];
+            sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);
+        }
+        __syncthreads();
+        // ---- fc2: 3 k-slices x 84 outputs, 4 images per weight load
         if (tid < 3 * G::F2) {
             const int j = tid % G::F2, ks = tid / G::F2;
             const float* wp = W + L3.w_off + (size_t)(ks * 40) * G::F2 + j;
-            float a = 0.f;
+            float a[kGI];
+#pragma unroll
+            for (int g = 0; g < kGI; g++) a[g] = 0.f;
 #pragma unroll 8
-            for (int k = 0; k < 40; k++) a = fmaf(sm[G::S_H1 + ks * 40 + k], __ldg(wp + (size_t)k * G::F2), a);
-            sm[G::S_H2 + ks * G::F2 + j] = a;
+            for (int k = 0; k < 40; k++) {
+                const float w = __ldg(wp + (size_t)k * G::F2);
+#pragma unroll
+                for (int g = 0; g < kGI; g++) a[g] = fmaf(sm[G::S_H1 + g * G::F1 + ks * 40 + k], w, a[g]);
+            }
+#pragma unroll
+            for (int g = 0; g < kGI; g++) sm[G::S_H2 + (g * 3 + ks) * G::F2 + j] = a[g];
         }
         __syncthreads();
-        if (tid < G::F2) {
-            const float v = sm[G::S_H2 + tid] + sm[G::S_H2 + G::F2 + tid] + sm[G::S_H2 + 2 * G::F2 + tid] + __ldg(W + L3.b_off + tid);
-            sm[G::S_H1 + tid] = fmaxf(v, 0.f);  // h2 reuses the h1 area (fc2 has finished reading it)
+        for (int o = tid; o < kGI * G::F2; o += kGT) {
+            const int g = o / G::F2, j = o % G::F2;
+            const float v = sm[G::S_H2 + (g * 3) * G::F2 + j] + sm[G::S_H2 + (g * 3 + 1) * G::F2 + j] +
+                            sm[G::S_H2 + (g * 3 + 2) * G::F2 + j] + __ldg(W + L3.b_off + j);
+            sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);  // h2 reuses the h1 area (fc2 has finished reading it)
         }
         __syncthreads();
-        // ---- fc3 + softmax / argmax: warp 0, lane = class
-        if (tid < 32) {
+        // ---- fc3 + softmax / argmax: warp g handles image g, lane = class
+        const int g = tid >> 5, lane = tid & 31;
+        if (g < imgs) {
+            const int img = list[it + g];
             float x = -INFINITY;
-            if (tid < G::F3) {
-                float a = __ldg(W + L4.b_off + tid);
-                const float* wp = W + L4.w_off + tid;
+            if (lane < G::F3) {
+                float a = __ldg(W + L4.b_off + lane);
+                const float* wp = W + L4.w_off + lane;
 #pragma unroll 4
-                for (int k = 0; k < G::F2; k++) a = fmaf(sm[G::S_H1 + k], __ldg(wp + (size_t)k * G::F3), a);
+                for (int k = 0; k < G::F2; k++) a = fmaf(sm[G::S_H1 + g * G::F1 + k], __ldg(wp + (size_t)k * G::F3), a);
                 x = a;
             }
             float mx = x;
-            int am = tid;
+            int am = lane;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 const float ox = __shfl_xor_sync(0xffffffffu, mx, o);
                 const int oa = __shfl_xor_sync(0xffffffffu, am, o);
                 if (ox > mx || (ox == mx && oa < am)) { mx = ox; am = oa; }
             }
-            const float e = tid < G::F3 ? expf(x - mx) : 0.f;
+            const float e = lane < G::F3 ? expf(x - mx) : 0.f;
             float s = e;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (tid < G::F3) {
-                probs[(size_t)img * G::F3 + tid] = e / s;
-                if (logits) logits[(size_t)img * G::F3 + tid] = x;
+            if (lane < G::F3) {
+                probs[(size_t)img * G::F3 + lane] = e / s;
+                if (logits) logits[(size_t)img * G::F3 + lane] = x;
             }
-            if (tid == 0 && argmax) argmax[img] = am;
+            if (lane == 0 && argmax) argmax[img] = am;
         }
     }
 }
@@ -220,8 +245,7 @@ int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected,
         configured[dev & 63] = true;
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int per_sm = max(1, min(6, (200 * 1024) / smem));
-    const int grid = max(1, min(expected, sms * per_sm));
+    const int grid = max(1, min((expected + kGI - 1) / kGI, sms * 2));
     guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, d_list, d_count, cap, d_probs, d_logits, d_argmax);
     return (int)cudaGetLastError();
 }
