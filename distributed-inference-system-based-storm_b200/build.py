@@ -19,7 +19,7 @@ SOURCES = ["sib_model.cpp", "sib_json.cpp", "sib_engine.cpp", "sib_abi.cpp", "si
            "sib_kernels_fp32.cu", "sib_kernels_tc.cu", "sib_kernels_guard.cu", "sib_static_scratch.cu", "sib_kernels_json.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler",
-         "-fPIC,-Wall,-Wno-unused-function", "-ccbin", "/usr/bin/g++"]
+         "-fPIC,-Wall,-Wno-unused-function", "-ccbin", "/usr/bin/g++"] + os.environ.get("SIB_NVCC_EXTRA", "").split()
 
 
 def _newest_header() -> float:

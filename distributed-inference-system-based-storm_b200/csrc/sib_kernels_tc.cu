@@ -34,11 +34,27 @@
 namespace sib {
 namespace {
 
-// 12 warps = 3 per SM sub-partition, so each thread may hold 168 registers (the register file is split per
-// sub-partition: a 4th warp there would cap every thread at 128 and spill the sliding windows).
-// Sub-partition = warp % 4: each gets 2 conv1 warps + (a conv2 warp | the fc warp): 245*2+333 vs 245*2+256 mma / 8 images.
-constexpr int kConv1Warps = 8;
-constexpr int kConv2Warps = 3;
+// Warp layout. The register file is split per SM sub-partition (warp % 4): 3 warps there may hold 168 registers
+// each, 4 warps only 128. Two layouts were measured (tools/sweep_tc.sh, profiles/ncu_tc_r01_notes.md):
+//   8 conv1 + 3 conv2 + 1 fc, 168 regs, two 4-row prefetch batches, split accumulator chains: 205 M img/s
+//  12 conv1 + 3 conv2 + 1 fc, 128 regs, two 2-row prefetch batches, single chains (fits with 8 B spill): 216 M img/s
+// The second is the default: a 4th warp per sub-partition hides more of the mma / shared-memory latency than the
+// extra registers bought. Each sub-partition hosts 3 conv1 warps + (a conv2 warp | the fc warp).
+#ifndef SIB_CONV1_WARPS
+#define SIB_CONV1_WARPS 12
+#endif
+#ifndef SIB_BATCH_ROWS
+#define SIB_BATCH_ROWS 2
+#endif
+#ifndef SIB_SPLIT_ACC
+#define SIB_SPLIT_ACC 0
+#endif
+constexpr int kConv1Warps = SIB_CONV1_WARPS;
+constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two batches in flight)
+#ifndef SIB_CONV2_WARPS
+#define SIB_CONV2_WARPS 3
+#endif
+constexpr int kConv2Warps = SIB_CONV2_WARPS;
 constexpr int kFcWarps = 1;
 constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps;
 constexpr int kThreadsTc = kWarps * 32;
@@ -73,7 +89,7 @@ struct Net {
     static constexpr int PD = REG_STAGE ? 8 : 7;                    // rows in flight per conv1 warp
     static constexpr int NCHUNK = (40 * C + 3) / 4;                 // 16-byte chunks per staged span row
     static constexpr int RING_ROW = ((40 * C + 16 + 7) / 8) * 8;    // halves per staged row incl. zero slack
-    static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && H % PD == 0, "tiling");
+    static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && H % PD == 0 && (!REG_STAGE || H % (2 * kBR) == 0), "tiling");
     static_assert(K1ROW <= 15 && NCHUNK <= 32 && OW1 % 2 == 0 && OW2 % 2 == 0 && W % 4 == 0 && ROWF % 4 == 0, "layout");
     // packed weight image (32-bit words)
     static constexpr int W_C1 = 0;                               // [2 variants][5 kh][32 lanes][2]
@@ -239,12 +255,12 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
     span_src(gs, img0, valid);
     if (!valid) return;
     const float* src = chunk_ptr(img0, gs % N::SPANS);
-    float4 preA[4], preB[4];  // REG_STAGE: rows 8k..8k+3 / 8k+4..8k+7 of the span, one 16-byte chunk per lane
+    float4 preA[kBR], preB[kBR];  // REG_STAGE: two batches of kBR consecutive rows, one 16-byte chunk per lane
     if constexpr (N::REG_STAGE) {
 #pragma unroll
-        for (int r = 0; r < 4; r++) preA[r] = ldg_stream(src + r * N::ROWF);
+        for (int r = 0; r < kBR; r++) preA[r] = ldg_stream(src + r * N::ROWF);
 #pragma unroll
-        for (int r = 0; r < 4; r++) preB[r] = ldg_stream(src + (4 + r) * N::ROWF);
+        for (int r = 0; r < kBR; r++) preB[r] = ldg_stream(src + (kBR + r) * N::ROWF);
     } else {
 #pragma unroll
         for (int r = 0; r < N::PD; r++) {
@@ -282,7 +298,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         auto stage_row = [&](int r) {
             float4 v;
             if constexpr (N::REG_STAGE) {
-                v = ((r >> 2) & 1) ? preB[r & 3] : preA[r & 3];
+                v = ((r / kBR) & 1) ? preB[r % kBR] : preA[r % kBR];
             } else {
                 cp_async_wait<N::PD - 1>();
                 v = lds128(stage + (r % N::PD) * N::STAGE_ROW);  // bytes this lane copied itself
@@ -295,11 +311,11 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             // address even when there is no next span, so the loads need no branch)
             auto row_ptr = [&](int row) { return row < N::H ? src + row * N::ROWF : n_src + (row - N::H) * N::ROWF; };
             if constexpr (N::REG_STAGE) {
-                if ((r & 3) == 3) {  // batch drained: fetch the batch two ahead (rows r+5 .. r+8) in one burst
+                if (r % kBR == kBR - 1) {  // batch drained: fetch the batch two ahead in one burst
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const float4 nv = ldg_stream(row_ptr(r + 5 + j));
-                        if ((r >> 2) & 1) preB[j] = nv; else preA[j] = nv;
+                    for (int j = 0; j < kBR; j++) {
+                        const float4 nv = ldg_stream(row_ptr(r + kBR + 1 + j));
+                        if ((r / kBR) & 1) preB[j] = nv; else preA[j] = nv;
                     }
                 }
             } else {
@@ -334,9 +350,9 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
                 const int oh = h - 4;
                 // kernel row 0 first: it reads the window slot that row h+1 is about to overwrite
                 Ops<T>::mma(cE, aE[(oh + 0) % 5], bE[0]); Ops<T>::mma(cO, aO[(oh + 0) % 5], bO[0]);
-                Ops<T>::mma(dE, aE[(oh + 3) % 5], bE[3]); Ops<T>::mma(dO, aO[(oh + 3) % 5], bO[3]);
+                Ops<T>::mma(SIB_SPLIT_ACC ? dE : cE, aE[(oh + 3) % 5], bE[3]); Ops<T>::mma(SIB_SPLIT_ACC ? dO : cO, aO[(oh + 3) % 5], bO[3]);
                 Ops<T>::mma(cE, aE[(oh + 1) % 5], bE[1]); Ops<T>::mma(cO, aO[(oh + 1) % 5], bO[1]);
-                Ops<T>::mma(dE, aE[(oh + 4) % 5], bE[4]); Ops<T>::mma(dO, aO[(oh + 4) % 5], bO[4]);
+                Ops<T>::mma(SIB_SPLIT_ACC ? dE : cE, aE[(oh + 4) % 5], bE[4]); Ops<T>::mma(SIB_SPLIT_ACC ? dO : cO, aO[(oh + 4) % 5], bO[4]);
                 Ops<T>::mma(cE, aE[(oh + 2) % 5], bE[2]); Ops<T>::mma(cO, aO[(oh + 2) % 5], bO[2]);
             }
             if (h + 1 < N::H) load_frags(h + 1);
