@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 
 #include <cstring>
+#include <type_traits>
 #include <vector>
 
 #include "sib_internal.hpp"
@@ -40,8 +41,11 @@ namespace {
 //  12 conv1 + 3 conv2 + 1 fc, 128 regs, two 2-row prefetch batches, single chains (fits with 8 B spill): 216 M img/s
 // The second is the default: a 4th warp per sub-partition hides more of the mma / shared-memory latency than the
 // extra registers bought. Each sub-partition hosts 3 conv1 warps + (a conv2 warp | the fc warp).
+#ifndef SIB_CONV1_UMMA
+#define SIB_CONV1_UMMA 0   // 1: conv1 on tcgen05.mma with operands in TMEM (sib_tc_conv1_umma.cuh)
+#endif
 #ifndef SIB_CONV1_WARPS
-#define SIB_CONV1_WARPS 12
+#define SIB_CONV1_WARPS (SIB_CONV1_UMMA ? 8 : 12)
 #endif
 #ifndef SIB_BATCH_ROWS
 #define SIB_BATCH_ROWS 2
@@ -52,11 +56,12 @@ namespace {
 constexpr int kConv1Warps = SIB_CONV1_WARPS;
 constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two batches in flight)
 #ifndef SIB_CONV2_WARPS
-#define SIB_CONV2_WARPS 3
+#define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
 constexpr int kFcWarps = 1;
-constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps;
+constexpr int kIssueWarps = SIB_CONV1_UMMA ? 2 : 0;  // one tcgen05.mma issuer per conv1 warpgroup
+constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps + kIssueWarps;
 constexpr int kThreadsTc = kWarps * 32;
 constexpr int kG = 8;     // images per ring slot (conv stages)
 constexpr int kPair = 16; // images per fc M tile = 2 slots
@@ -89,7 +94,7 @@ struct Net {
     static constexpr int PD = REG_STAGE ? 8 : 7;                    // rows in flight per conv1 warp
     static constexpr int NCHUNK = (40 * C + 3) / 4;                 // 16-byte chunks per staged span row
     static constexpr int RING_ROW = ((40 * C + 16 + 7) / 8) * 8;    // halves per staged row incl. zero slack
-    static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && H % PD == 0 && (!REG_STAGE || H % (2 * kBR) == 0), "tiling");
+    static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && (SIB_CONV1_UMMA || H % PD == 0) && ((!REG_STAGE && !SIB_CONV1_UMMA) || H % (2 * kBR) == 0), "tiling");
     static_assert(K1ROW <= 15 && NCHUNK <= 32 && OW1 % 2 == 0 && OW2 % 2 == 0 && W % 4 == 0 && ROWF % 4 == 0, "layout");
     // packed weight image (32-bit words)
     static constexpr int W_C1 = 0;                               // [2 variants][5 kh][32 lanes][2]
@@ -99,21 +104,27 @@ struct Net {
     static constexpr int W_F2 = W_F1 + KS1 * NT1 * 64;           // [8 ks][12 nt][32][2]
     static constexpr int W_F3 = W_F2 + 8 * 12 * 64;              // [6 ks][2 nt][32][2]
     static constexpr int W_BIAS = W_F3 + 6 * 2 * 64;             // fp32: c1[8] c2[16] f1[128] f2[96] f3[16]
-    static constexpr int W_TOTAL = W_BIAS + 8 + 16 + 128 + 96 + 16;
+    static constexpr int W_C1U = W_BIAS + 8 + 16 + 128 + 96 + 16;  // conv1 as tcgen05 B operands: [even|odd][5 kh][16 n][16 k] halves
+    static constexpr int W_TOTAL = W_C1U + 2 * 5 * 128;
     // shared memory map (bytes)
     static constexpr int S_FCW = 0;                                        // fc1|fc2|fc3 fragments
     static constexpr int S_FCW_BYTES = (W_BIAS - W_F1) * 4;
     static constexpr int S_BIAS = S_FCW + S_FCW_BYTES;                     // 264 floats
-    static constexpr int S_P1 = S_BIAS + 264 * 4;
+    static constexpr int S_B1U = ((S_BIAS + 264 * 4 + 127) / 128) * 128;   // conv1 B operands for tcgen05 (5 KB)
+    static constexpr int S_P1 = SIB_CONV1_UMMA ? S_B1U + 2 * 5 * 512 : S_BIAS + 264 * 4;
     static constexpr int S_P2 = S_P1 + NB1 * P1_BUF * 2;
     static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
     static constexpr int S_H2 = S_H1 + kPair * H1_STRIDE * 2;
     static constexpr int S_RING = S_H2 + kPair * H2_STRIDE * 2;
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
-    static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * RING_ROW * 2; // cp.async landing zone: PD rows per conv1 warp
-    static constexpr int S_BAR = S_STAGE + (REG_STAGE ? 0 : kConv1Warps * PD * STAGE_ROW);
-    static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2, N_BAR = 2 * NB1 + 4;
-    static constexpr int S_TOTAL = S_BAR + N_BAR * 8;
+    static constexpr int URING_ROW = 80 * C + 16;                          // halves: Umma<N>::UROW
+    static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * (SIB_CONV1_UMMA ? URING_ROW : RING_ROW) * 2; // cp.async landing zone
+    static constexpr int S_BAR = ((S_STAGE + ((REG_STAGE || SIB_CONV1_UMMA) ? 0 : kConv1Warps * PD * STAGE_ROW) + 7) / 8) * 8;
+    static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2;
+    static constexpr int B_UA = 2 * NB1 + 4, B_UDF = B_UA + 12, B_UDE = B_UDF + 4;  // tcgen05 conv1: a_full[2][6], d_full[2][2], d_empty[2][2]
+    static constexpr int N_BAR = SIB_CONV1_UMMA ? B_UDE + 4 : 2 * NB1 + 4;
+    static constexpr int S_TMEM = S_BAR + N_BAR * 8;                       // TMEM base address handed out by tcgen05.alloc
+    static constexpr int S_TOTAL = S_TMEM + 8;
     static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_STAGE % 16 == 0 && S_BAR % 8 == 0, "align");
     static_assert(S_TOTAL <= 227 * 1024, "shared memory");
 };
@@ -207,7 +218,12 @@ struct TcParams {
     float* dbg;      // may be null: CTA 0 dumps p1/p2/h1/h2 of its first 16 images (tests)
 };
 
-// ---- conv1 role ---------------------------------------------------------------------------------------------
+#if SIB_CONV1_UMMA
+#include "sib_tc_umma.cuh"
+#include "sib_tc_conv1_umma.cuh"
+#endif
+
+// ---- conv1 role (mma.sync form) ------------------------------------------------------------------------------
 
 template <typename N, typename T, bool DBG>
 __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* smem, int cw, int lane) {
@@ -659,10 +675,24 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
         for (int i = threadIdx.x; i < 264; i += blockDim.x) b[i] = reinterpret_cast<const float*>(P.wpack + N::W_BIAS)[i];
         uint32_t* z = reinterpret_cast<uint32_t*>(smem + N::S_P1);
         for (int i = threadIdx.x; i < (N::S_BAR - N::S_P1) / 4; i += blockDim.x) z[i] = 0u;  // p1,p2,h1,h2,rings
+#if SIB_CONV1_UMMA
+        {
+            const uint4* bs = reinterpret_cast<const uint4*>(P.wpack + N::W_C1U);
+            uint4* bd = reinterpret_cast<uint4*>(smem + N::S_B1U);
+            for (int i = threadIdx.x; i < 2 * 5 * 512 / 16; i += blockDim.x) bd[i] = bs[i];
+        }
+        __syncwarp();
+        if (warp == 0) tmem_alloc_all(reinterpret_cast<uint32_t*>(smem + N::S_TMEM));
+#endif
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+#if SIB_CONV1_UMMA
+            for (int i = 0; i < 12; i++) mbar_init(&bars[N::B_UA + i], 128);    // a_full : every thread of the warpgroup
+            for (int i = 0; i < 4; i++) mbar_init(&bars[N::B_UDF + i], 1);      // d_full : one tcgen05.commit
+            for (int i = 0; i < 4; i++) mbar_init(&bars[N::B_UDE + i], 128);    // d_empty: every thread of the warpgroup
+#endif
             for (int i = 0; i < N::NB1; i++) {
-                mbar_init(&bars[N::B_P1F + i], N::SPANS * 32);        // p1_full : every lane of every span
+                mbar_init(&bars[N::B_P1F + i], SIB_CONV1_UMMA ? 128 : N::SPANS * 32);  // p1_full : every conv1 lane working on the slot
                 mbar_init(&bars[N::B_P1E + i], N::TILES2 * 32);       // p1_empty: every lane of every conv2 tile
             }
             for (int i = 0; i < 2; i++) {
@@ -671,10 +701,24 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
             }
         }
     }
+#if SIB_CONV1_UMMA
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + N::S_TMEM);
+    if (warp < kConv1Warps) conv1u_worker<N, T, DBG>(P, smem, warp >> 2, warp & 3, lane, tmem);
+    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
+    else if (warp < kConv1Warps + kConv2Warps + kFcWarps) fc_role<N, T, DBG>(P, smem, lane);
+    else conv1u_issuer<N, T>(P, smem, warp - kConv1Warps - kConv2Warps - kFcWarps, tmem);
+    tc5_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_free_all(tmem);
+#else
     __syncthreads();
     if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
     else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
     else fc_role<N, T, DBG>(P, smem, lane);
+#endif
 }
 
 // ---- host side: weight packing ----------------------------------------------------------------------------------
@@ -727,6 +771,17 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
     dense(N::W_F1, N::KS1, N::NT1, L[2]);
     dense(N::W_F2, 8, 12, L[3]);
     dense(N::W_F3, 6, 2, L[4]);
+    // conv1 as tcgen05 B operands: canonical K-major no-swizzle tiles [n/8][k/8][n%8][k%8] of halves
+    for (int v = 0; v < 2; v++)
+        for (int kh = 0; kh < 5; kh++) {
+            uint16_t* dst = reinterpret_cast<uint16_t*>(&w[N::W_C1U + (v * 5 + kh) * 128]);
+            for (int n = 0; n < 16; n++)
+                for (int k = 0; k < 16; k++) {
+                    const int j = k - v;
+                    const float x = (j < 0 || j >= N::K1ROW || n >= N::C1) ? 0.f : f1[((kh * 5 + j / N::C) * N::C + j % N::C) * N::C1 + n];
+                    dst[(n / 8) * 128 + (k / 8) * 64 + (n % 8) * 8 + (k % 8)] = Ops<T>::host_bits(x);
+                }
+        }
     float* b = reinterpret_cast<float*>(&w[N::W_BIAS]);
     std::memcpy(b, wt + L[0].b_off, 6 * 4);
     std::memcpy(b + 8, wt + L[1].b_off, 16 * 4);
