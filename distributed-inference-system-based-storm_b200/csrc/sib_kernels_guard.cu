@@ -1,4 +1,4 @@
-// sib_kernels_guard.cu -- the margin guard's recompute path: fp32 CUDA-core LeNet-5 forward, up to four listed images per CTA pass.
+// sib_kernels_guard.cu -- the margin guard's recompute path: fp32 CUDA-core LeNet-5 forward, up to five listed images per CTA pass.
 //
 // The tensor-core kernel lists the images whose top1-top2 logit margin is below tau (sib_kernels_tc.cu); this
 // kernel re-runs exactly those images in fp32 and overwrites their outputs, so that the emitted argmax equals the
@@ -13,9 +13,15 @@
 namespace sib {
 namespace {
 
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 constexpr int kGT = 256;
-constexpr int kGI = 4;  // images per CTA pass: the dense weights stream from L2 once per 4 images, and the conv
-                        // stages have 4x the work items to spread over the 256 threads
+constexpr int kGI = 5;  // images per CTA pass: the dense weights stream from L2 once per 5 images, and 5 images give
+                        // 980 conv1 / 500 conv2 work items = 3.83 / 1.95 rounds of the 256 threads (4 images left a
+                        // quarter of the last conv1 round and half of the last conv2 round idle: r01 guard profile)
 
 template <int H_, int W_, int C_>
 struct GNet {
@@ -25,11 +31,13 @@ struct GNet {
     static constexpr int IMG = H * W * C, P1 = PH1 * PW1 * C1, FEAT = PH2 * PW2 * C2;
     static constexpr int NW1 = 25 * C * C1, NW2 = 25 * C1 * C2;
     static constexpr int KSL = 8;  // k slices of fc1
-    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && 3 * F2 <= kGT && kGI * 32 <= kGT, "mapping");
-    // shared memory (floats)
-    static constexpr int S_IMG = 0, S_W1 = S_IMG + kGI * IMG, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
-                         S_W2 = S_P1 + kGI * P1, S_P2 = S_W2 + NW2 + C2, S_PART = S_P2 + kGI * FEAT,
-                         S_H1 = S_PART + kGI * KSL * F1, S_H2 = S_H1 + kGI * F1, S_TOTAL = S_H2 + kGI * 3 * F2;
+    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && 3 * F2 <= kGT && kGI * 32 <= kGT && F2 % 3 == 0, "mapping");
+    // shared memory (floats). The images are dead once conv1 has run: the dense stages' scratch overlays them.
+    static constexpr int DENSE = kGI * KSL * F1 + kGI * F1 + kGI * 3 * F2;
+    static constexpr int S_IMG = 0, S_PART = 0, S_H1 = S_PART + kGI * KSL * F1, S_H2 = S_H1 + kGI * F1,
+                         S_W1 = ((kGI * IMG > DENSE ? kGI * IMG : DENSE) + 3) / 4 * 4, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
+                         S_W2 = S_P1 + kGI * P1, S_P2 = S_W2 + NW2 + C2, S_W3 = S_P2 + kGI * FEAT,
+                         S_TOTAL = S_W3 + F2 * F3 + F3 + 2;
 };
 
 template <typename G>
@@ -41,23 +49,38 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x;
     const int n = min(*count, cap);
+    // The list is dealt out in contiguous, near-equal shares (they differ by at most one image), so every CTA is done
+    // after the same number of passes; dealing whole 4-image passes round-robin left a second, mostly empty wave.
+    const int per = n / (int)gridDim.x, rem = n % (int)gridDim.x;
+    const int first = (int)blockIdx.x * per + min((int)blockIdx.x, rem), last = first + per + ((int)blockIdx.x < rem ? 1 : 0);
+    if (first >= last) return;
     const float* W = m.weights;
     const DeviceLayer L0 = m.layer[0], L1 = m.layer[1], L2 = m.layer[2], L3 = m.layer[3], L4 = m.layer[4];
-    // conv filters + biases stay in shared memory for every image this CTA handles
+    auto load_images = [&](int it, int imgs) {  // asynchronous copies: nothing waits until cp_async_wait_all()
+        for (int g = 0; g < kGI; g++) {          // rows past the end of the share repeat its last image (results dropped)
+            const int img = list[it + min(g, imgs - 1)];
+            const float* src = in + (size_t)img * G::IMG;
+            float* dst = sm + G::S_IMG + g * G::IMG;
+            for (int i = tid; i < G::IMG / 4; i += kGT) cp_async16(dst + 4 * i, src + 4 * i);
+        }
+    };
+    load_images(first, min(kGI, last - first));
+    // conv filters, fc3 and their biases stay in shared memory for every image this CTA handles (their load latency
+    // runs under the image copies above)
     for (int i = tid; i < G::NW1; i += kGT) sm[G::S_W1 + i] = __ldg(W + L0.w_off + i);
     for (int i = tid; i < G::C1; i += kGT) sm[G::S_W1 + G::NW1 + i] = __ldg(W + L0.b_off + i);
     for (int i = tid; i < G::NW2; i += kGT) sm[G::S_W2 + i] = __ldg(W + L1.w_off + i);
     for (int i = tid; i < G::C2; i += kGT) sm[G::S_W2 + G::NW2 + i] = __ldg(W + L1.b_off + i);
+    for (int i = tid; i < G::F2 * G::F3; i += kGT) sm[G::S_W3 + i] = __ldg(W + L4.w_off + i);
+    for (int i = tid; i < G::F3; i += kGT) sm[G::S_W3 + G::F2 * G::F3 + i] = __ldg(W + L4.b_off + i);
 
-    for (int it = blockIdx.x * kGI; it < n; it += gridDim.x * kGI) {
-        const int imgs = min(kGI, n - it);
-        __syncthreads();
-        for (int g = 0; g < kGI; g++) {  // rows past the end of the list repeat the last image (results dropped)
-            const int img = list[it + min(g, imgs - 1)];
-            const float4* s4 = reinterpret_cast<const float4*>(in + (size_t)img * G::IMG);
-            float4* d4 = reinterpret_cast<float4*>(sm + G::S_IMG + g * G::IMG);
-            for (int i = tid; i < G::IMG / 4; i += kGT) d4[i] = __ldg(s4 + i);
+    for (int it = first; it < last; it += kGI) {
+        const int imgs = min(kGI, last - it);
+        if (it != first) {
+            __syncthreads();  // the dense scratch of the previous pass overlays the image area
+            load_images(it, imgs);
         }
+        cp_async_wait_all();
         __syncthreads();
         // ---- conv1 + bias + ReLU + pool: item = (image, pooled position); 2x2 positions x 6 channels in registers
         for (int item = tid; item < kGI * G::PH1 * G::PW1; item += kGT) {
@@ -143,7 +166,7 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             }
         }
         __syncthreads();
-        // ---- fc1: 8 k-slices x 30 float4 columns; each 128-bit weight load from L2 serves the 4 images
+        // ---- fc1: 8 k-slices x 30 float4 columns; each 128-bit weight load from L2 serves all the images of the pass
         if (tid < G::KSL * (G::F1 / 4)) {
             const int n4 = tid % (G::F1 / 4), ks = tid / (G::F1 / 4);
             constexpr int KL = G::FEAT / G::KSL;
@@ -175,7 +198,7 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);
         }
         __syncthreads();
-        // ---- fc2: 3 k-slices x 84 outputs, 4 images per weight load
+        // ---- fc2: 3 k-slices x 84 outputs, one weight load per k for all the images of the pass
         if (tid < 3 * G::F2) {
             const int j = tid % G::F2, ks = tid / G::F2;
             const float* wp = W + L3.w_off + (size_t)(ks * 40) * G::F2 + j;
@@ -199,18 +222,21 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);  // h2 reuses the h1 area (fc2 has finished reading it)
         }
         __syncthreads();
-        // ---- fc3 + softmax / argmax: warp g handles image g, lane = class
+        // ---- fc3 + softmax / argmax: warp g handles image g; lane = (k third, class), thirds summed by shuffles
         const int g = tid >> 5, lane = tid & 31;
         if (g < imgs) {
             const int img = list[it + g];
-            float x = -INFINITY;
-            if (lane < G::F3) {
-                float a = __ldg(W + L4.b_off + lane);
-                const float* wp = W + L4.w_off + lane;
-#pragma unroll 4
-                for (int k = 0; k < G::F2; k++) a = fmaf(sm[G::S_H1 + g * G::F1 + k], __ldg(wp + (size_t)k * G::F3), a);
-                x = a;
+            constexpr int KT = G::F2 / 3;
+            const int cls = lane % G::F3, kt = min(lane / G::F3, 2);
+            float a = 0.f;
+            {
+                const float* hp = sm + G::S_H1 + g * G::F1 + kt * KT;
+                const float* wp = sm + G::S_W3 + (kt * KT) * G::F3 + cls;
+#pragma unroll 7
+                for (int k = 0; k < KT; k++) a = fmaf(hp[k], wp[k * G::F3], a);
             }
+            const float a1 = __shfl_down_sync(0xffffffffu, a, G::F3), a2 = __shfl_down_sync(0xffffffffu, a, 2 * G::F3);
+            const float x = lane < G::F3 ? (a + a1) + a2 + sm[G::S_W3 + G::F2 * G::F3 + lane] : -INFINITY;
             float mx = x;
             int am = lane;
 #pragma unroll

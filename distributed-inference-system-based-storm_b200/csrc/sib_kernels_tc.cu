@@ -117,12 +117,12 @@ struct Net {
     static constexpr int S_H2 = S_H1 + kPair * H1_STRIDE * 2;
     static constexpr int S_RING = S_H2 + kPair * H2_STRIDE * 2;
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
-    static constexpr int URING_ROW = 80 * C + 16;                          // halves: Umma<N>::UROW
+    static constexpr int URING_ROW = 2 * W * C + 16;                       // halves: Umma<N>::UROW
     static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * (SIB_CONV1_UMMA ? URING_ROW : RING_ROW) * 2; // cp.async landing zone
     static constexpr int S_BAR = ((S_STAGE + ((REG_STAGE || SIB_CONV1_UMMA) ? 0 : kConv1Warps * PD * STAGE_ROW) + 7) / 8) * 8;
     static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2;
-    static constexpr int B_UA = 2 * NB1 + 4, B_UDF = B_UA + 12, B_UDE = B_UDF + 4;  // tcgen05 conv1: a_full[2][6], d_full[2][2], d_empty[2][2]
-    static constexpr int N_BAR = SIB_CONV1_UMMA ? B_UDE + 4 : 2 * NB1 + 4;
+    static constexpr int B_UA = 2 * NB1 + 4, B_UDF = B_UA + 16, B_UDE = B_UDF + 8;  // tcgen05 conv1: a_full[2][8], d_full[2][4], d_empty[2][4]
+    static constexpr int N_BAR = SIB_CONV1_UMMA ? B_UDE + 8 : 2 * NB1 + 4;
     static constexpr int S_TMEM = S_BAR + N_BAR * 8;                       // TMEM base address handed out by tcgen05.alloc
     static constexpr int S_TOTAL = S_TMEM + 8;
     static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_STAGE % 16 == 0 && S_BAR % 8 == 0, "align");
@@ -687,9 +687,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
 #if SIB_CONV1_UMMA
-            for (int i = 0; i < 12; i++) mbar_init(&bars[N::B_UA + i], 128);    // a_full : every thread of the warpgroup
-            for (int i = 0; i < 4; i++) mbar_init(&bars[N::B_UDF + i], 1);      // d_full : one tcgen05.commit
-            for (int i = 0; i < 4; i++) mbar_init(&bars[N::B_UDE + i], 128);    // d_empty: every thread of the warpgroup
+            for (int i = 0; i < 16; i++) mbar_init(&bars[N::B_UA + i], 128);    // a_full : every thread of the warpgroup
+            for (int i = 0; i < 8; i++) mbar_init(&bars[N::B_UDF + i], 1);      // d_full : one tcgen05.commit
+            for (int i = 0; i < 8; i++) mbar_init(&bars[N::B_UDE + i], 128);    // d_empty: every thread of the warpgroup
 #endif
             for (int i = 0; i < N::NB1; i++) {
                 mbar_init(&bars[N::B_P1F + i], SIB_CONV1_UMMA ? 128 : N::SPANS * 32);  // p1_full : every conv1 lane working on the slot

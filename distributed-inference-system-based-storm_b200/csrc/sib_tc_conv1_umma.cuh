@@ -10,23 +10,30 @@
 // 2q and 2q+1 of the slot's column space (224 | 192 columns a row), i.e. TMEM lane q of an "even" and an "odd"
 // M=128 tile (odd columns read their 16 K values one element early against filters shifted by one: every
 // shared-memory read stays 4-byte aligned, and the 2x2 pool never leaves the thread).
-//   per input row h:  stage the row (fp32 -> half, warp-private)  ->  16 x LDS.32 -> 2 x tcgen05.st (A_e(h), A_o(h))
-//                     -> arrive on a_full[h % 6]
+//   per input row h:  stage the row (fp32 -> half, warp-private)  ->  LDS.32 -> 2 x tcgen05.st (A_e(h), A_o(h))
+//                     -> arrive on a_full[row % 8]
 //   issuer warp    :  once rows oh..oh+4 are in TMEM: D_t(oh) = sum_kh A_t(oh+kh) . B_t,kh  (10 mma, t = even|odd)
-//                     -> tcgen05.commit -> d_full[oh & 1]
-//   one row later  :  tcgen05.ld D_e, D_o -> max (column pair) -> max with the previous row -> +bias, ReLU -> p1
-// TMEM per warpgroup: 6 input rows x (8 + 8) columns + 2 output rows x (16 + 16) columns = 160 of the 512 columns.
+//                     -> tcgen05.commit -> d_full[oh % 4]
+//   kLag rows later:  tcgen05.ld D_e, D_o -> max (column pair) -> max with the previous row -> +bias, ReLU -> p1
+// The epilogue trails the A rows by kLag = 2 rows so that the issuer's wake-up + 10 mma + commit (about 250 clk) runs
+// under the next row's staging instead of being waited for; its tcgen05.ld is issued first in a row and collected
+// after the row's tcgen05.st, so the two TMEM round trips overlap. A warp holds the column pairs of exactly two images
+// (28 | 24 live lanes): with one image seam per warp the 3-words-per-lane shared-memory reads never share a bank.
+// TMEM per warpgroup: 8 input rows x (8 + 8) columns + 4 output rows x (16 + 16) columns = 256 of the 512 columns.
 #pragma once
 
 template <typename N>
 struct Umma {
     static constexpr int NPOS = kG * N::OW1, NPAIR = NPOS / 2;       // output columns / column pairs per slot row
-    static constexpr int PXW = 80;                                    // input pixels one warp's 64 columns can touch
+    static constexpr int PPW = NPAIR / 4;                             // pairs per warp = the pairs of two images
+    static constexpr int PXW = 2 * N::W;                              // input pixels a warp stages per row: two image rows
     static constexpr int NCH = PXW * N::C / 4;                        // 16-byte chunks of a staged warp row
     static constexpr int CPL = (NCH + 31) / 32;                       // chunks per lane
-    static constexpr int UROW = PXW * N::C + 16;                      // halves per staged row incl. slack
-    static constexpr int TM_WG = 160, TM_A = 0, TM_D = 96;            // TMEM columns per warpgroup
-    static_assert(NPAIR <= 128 && N::OW1 % 2 == 0 && UROW % 8 == 0, "umma tiling");
+    static constexpr int UROW = PXW * N::C + 16;                      // halves per staged row incl. zero slack
+    static constexpr int NA = 8, ND = 4, kLag = 2;                    // A rows / D rows resident in TMEM, epilogue lag
+    static constexpr int TM_WG = 256, TM_A = 0, TM_D = NA * 16;       // TMEM columns per warpgroup
+    static_assert(NPAIR % 4 == 0 && PPW <= 32 && PPW == N::OW1 && UROW % 8 == 0 && UROW == N::URING_ROW, "umma tiling");
+    static_assert(N::H % 4 == 0 && N::OH1 % 4 == 0 && kBR == 2 && kLag <= NA - 5 && 2 * TM_WG <= 512, "umma pipeline");
 };
 
 // ---- worker warps (2 warpgroups) ------------------------------------------------------------------------------------
@@ -38,9 +45,9 @@ __device__ __forceinline__ void conv1u_worker(const TcParams& P, unsigned char* 
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
     uint64_t* p1_full = bars + N::B_P1F;
     uint64_t* p1_empty = bars + N::B_P1E;
-    uint64_t* a_full = bars + N::B_UA + wg * 6;
-    uint64_t* d_full = bars + N::B_UDF + wg * 2;
-    uint64_t* d_empty = bars + N::B_UDE + wg * 2;
+    uint64_t* a_full = bars + N::B_UA + wg * U::NA;
+    uint64_t* d_full = bars + N::B_UDF + wg * U::ND;
+    uint64_t* d_empty = bars + N::B_UDE + wg * U::ND;
     const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS);
     float bias[N::C1];
 #pragma unroll
@@ -48,28 +55,24 @@ __device__ __forceinline__ void conv1u_worker(const TcParams& P, unsigned char* 
     const uint32_t tm_lane = tmem + ((uint32_t)(quad * 32) << 16) + wg * U::TM_WG;  // this warp's lane quadrant, WG's columns
     const int nPairs = (P.n + kPair - 1) / kPair;
 
-    // this lane's column pair and where its 16 K values start in the warp's staged row
-    const int q = min(quad * 32 + lane, U::NPAIR - 1);
-    const bool live = quad * 32 + lane < U::NPAIR;
-    const int p_first = 64 * quad, p_last = min(64 * quad + 63, U::NPOS - 1);
-    const int u_start = (p_first / N::OW1) * N::W + p_first % N::OW1;
-    const int u_last = (p_last / N::OW1) * N::W + p_last % N::OW1 + 4;
-    const int nch = ((u_last + 1 - u_start) * N::C + 3) / 4;  // chunks this warp really needs
+    // this lane's column pair (lanes >= PPW shadow the last live lane; their tile rows are never read back)
+    const bool live = lane < U::PPW;
+    const int q = U::PPW * quad + min(lane, U::PPW - 1);
     const int pe = 2 * q;
     const int img_l = pe / N::OW1, ow = pe % N::OW1;
-    const int offE = (img_l * N::W + ow - u_start) * N::C;   // even column: halves offE .. offE+15
-    constexpr int kOdd = N::C - 1;                             // odd column: one element early (see header)
+    const int offE = ((img_l - 2 * quad) * N::W + ow) * N::C;  // even column: halves offE .. offE+15 of the staged row
+    constexpr int kOdd = N::C - 1;                               // odd column: one element early (see header)
     const int o_p1 = img_l * N::P1_IMG + (ow >> 1) * N::C1;
     const int o_dbg = img_l * N::PH1 * N::P1_ROW + (ow >> 1) * N::C1;
 
-    // chunk c of the warp row -> (image, offset in the image row)
+    // chunk c of the warp row -> (image, offset in the image row); the warp stages images 2*quad and 2*quad+1
     int c_img[U::CPL], c_rem[U::CPL];
     bool c_on[U::CPL];
 #pragma unroll
     for (int i = 0; i < U::CPL; i++) {
         const int c = lane + 32 * i;
-        c_on[i] = c < nch;
-        const int F0 = u_start * N::C + 4 * min(c, nch - 1);
+        c_on[i] = c < U::NCH;
+        const int F0 = 2 * quad * N::ROWF + 4 * min(c, U::NCH - 1);
         c_img[i] = F0 / N::ROWF;
         c_rem[i] = F0 % N::ROWF;
     }
@@ -107,20 +110,21 @@ __device__ __forceinline__ void conv1u_worker(const TcParams& P, unsigned char* 
         uint16_t* p1 = reinterpret_cast<uint16_t*>(smem + N::S_P1) + buf * N::P1_BUF;
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && lq < 2;
         mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
+        const int rbase = sd * N::H, gbase = sd * N::OH1;   // running A-row / D-row numbers (both multiples of 4)
 
         float prev[N::C1];
-        // epilogue of output row oh: D_e / D_o from TMEM, pool, bias, ReLU, pooled row -> p1
-        auto epilogue = [&](int oh) {
-            const int gd = sd * N::OH1 + oh, b = gd & 1;
-            mbar_wait(&d_full[b], (gd >> 1) & 1);
+        // the epilogue of output row oh in two halves: fetch (wait for the mma, start the TMEM loads) and finish
+        auto epi_fetch = [&](int oh, int b, float (&de)[8], float (&dod)[8]) {
+            mbar_wait(&d_full[b], ((gbase + oh) >> 2) & 1);
             tc5_fence_after();
-            float de[8], dod[8];
             tmem_ld8(tm_lane + U::TM_D + b * 32, de);
             tmem_ld8(tm_lane + U::TM_D + b * 32 + 16, dod);
+        };
+        auto epi_finish = [&](int oh, int b, bool odd, const float (&de)[8], const float (&dod)[8]) {
             tmem_wait_ld();
             tc5_fence_before();
             mbar_arrive(&d_empty[b]);
-            if ((oh & 1) == 0) {
+            if (!odd) {
 #pragma unroll
                 for (int c = 0; c < N::C1; c++) prev[c] = fmaxf(de[c], dod[c]);
             } else {
@@ -140,47 +144,63 @@ __device__ __forceinline__ void conv1u_worker(const TcParams& P, unsigned char* 
             }
         };
 
+#pragma unroll 1
+        for (int h0 = 0; h0 < N::H; h0 += 4) {
 #pragma unroll
-        for (int h = 0; h < N::H; h++) {
-            // ---- stage input row h (warp-private): fp32 chunks from the prefetch registers -> half
-            uint16_t* rr = ring + (h & 1) * U::UROW;
+            for (int j = 0; j < 4; j++) {  // everything that depends on h % 4 is a compile-time constant below
+                const int h = h0 + j;
+                const int oh = h - 4 - U::kLag;
+                const bool epi = oh >= 0;
+                constexpr int kL4 = U::kLag & 3;
+                const int b = (j + 4 - kL4) & 3;            // = oh % 4 (H, OH1 and 4 are all multiples of 4)
+                const bool odd = ((j + U::kLag) & 1) != 0;  // = oh % 2
+                float de[8], dod[8];
+                if (epi) epi_fetch(oh, b, de, dod);
+                // ---- stage input row h (warp-private): fp32 chunks from the prefetch registers -> half
+                uint16_t* rr = ring + (j & 1) * U::UROW;
 #pragma unroll
-            for (int i = 0; i < U::CPL; i++) {
-                const float4 v = ((h / kBR) & 1) ? preB[h % kBR][i] : preA[h % kBR][i];
-                if (c_on[i]) {
-                    uint2 pk;
-                    pk.x = Ops<T>::pack(v.x, v.y);
-                    pk.y = Ops<T>::pack(v.z, v.w);
-                    *reinterpret_cast<uint2*>(rr + 4 * (lane + 32 * i)) = pk;
-                }
-            }
-            if (h % kBR == kBR - 1) {  // batch drained: fetch the batch two ahead (may belong to the next slot)
-#pragma unroll
-                for (int j = 0; j < kBR; j++)
-#pragma unroll
-                    for (int i = 0; i < U::CPL; i++) {
-                        const float4 nv = ldg_stream(row_ptr(i, h + kBR + 1 + j));
-                        if ((h / kBR) & 1) preB[j][i] = nv; else preA[j][i] = nv;
+                for (int i = 0; i < U::CPL; i++) {
+                    const float4 v = ((j / kBR) & 1) ? preB[j % kBR][i] : preA[j % kBR][i];
+                    if (c_on[i]) {
+                        uint2 pk;
+                        pk.x = Ops<T>::pack(v.x, v.y);
+                        pk.y = Ops<T>::pack(v.z, v.w);
+                        *reinterpret_cast<uint2*>(rr + 4 * (lane + 32 * i)) = pk;
                     }
-            }
-            if ((lane & 7) == 0 && c_on[0] && (h + 16 < N::H || n_valid)) prefetch_l2(row_ptr(0, h + 16));
-            __syncwarp();
-            // ---- im2col rows of this lane's two columns -> TMEM (A_e(h) | A_o(h))
-            uint32_t ae[8], ao[8];
+                }
+                if (j % kBR == kBR - 1) {  // batch drained: fetch the batch two ahead (may belong to the next slot)
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
-                ae[k] = lds32(rr + offE + 2 * k);
-                ao[k] = lds32(rr + offE + kOdd + 2 * k);
+                    for (int jj = 0; jj < kBR; jj++)
+#pragma unroll
+                        for (int i = 0; i < U::CPL; i++) {
+                            const float4 nv = ldg_stream(row_ptr(i, h + kBR + 1 + jj));
+                            if ((j / kBR) & 1) preB[jj][i] = nv; else preA[jj][i] = nv;
+                        }
+                }
+                if ((lane & 7) == 0 && c_on[0] && (h + 16 < N::H || n_valid)) prefetch_l2(row_ptr(0, h + 16));
+                __syncwarp();
+                // ---- im2col rows of this lane's two columns -> TMEM (A_e(h) | A_o(h))
+                uint32_t ae[8], ao[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    ae[k] = lds32(rr + offE + 2 * k);
+                    ao[k] = lds32(rr + offE + kOdd + 2 * k);
+                }
+                const int slot = (rbase + h) & (U::NA - 1);
+                tmem_st8(tm_lane + U::TM_A + slot * 16, ae);
+                tmem_st8(tm_lane + U::TM_A + slot * 16 + 8, ao);
+                if (epi) epi_finish(oh, b, odd, de, dod);
+                tmem_wait_st();
+                tc5_fence_before();
+                mbar_arrive(&a_full[slot]);
             }
-            const int Rg = sd * N::H + h, slot = Rg % 6;
-            tmem_st8(tm_lane + U::TM_A + slot * 16, ae);
-            tmem_st8(tm_lane + U::TM_A + slot * 16 + 8, ao);
-            tmem_wait_st();
-            tc5_fence_before();
-            mbar_arrive(&a_full[slot]);
-            if (h >= 5) epilogue(h - 5);
         }
-        epilogue(N::H - 5);  // the last output row of the slot
+#pragma unroll
+        for (int oh = N::OH1 - U::kLag; oh < N::OH1; oh++) {  // the slot's last output rows
+            float de[8], dod[8];
+            epi_fetch(oh, oh & 3, de, dod);
+            epi_finish(oh, oh & 3, (oh & 1) != 0, de, dod);
+        }
         mbar_arrive(&p1_full[buf]);
     }
 }
@@ -191,9 +211,9 @@ template <typename N, typename T>
 __device__ __forceinline__ void conv1u_issuer(const TcParams& P, unsigned char* smem, int wg, uint32_t tmem) {
     using U = Umma<N>;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-    uint64_t* a_full = bars + N::B_UA + wg * 6;
-    uint64_t* d_full = bars + N::B_UDF + wg * 2;
-    uint64_t* d_empty = bars + N::B_UDE + wg * 2;
+    uint64_t* a_full = bars + N::B_UA + wg * U::NA;
+    uint64_t* d_full = bars + N::B_UDF + wg * U::ND;
+    uint64_t* d_empty = bars + N::B_UDE + wg * U::ND;
     const uint32_t b_base = smem_u32(smem + N::S_B1U);  // [even|odd][kh] 16x16 halves each, 512 bytes apart
     const uint32_t idesc = umma_idesc_m128_n16<T>();
     const uint32_t tm = tmem + wg * U::TM_WG;
@@ -202,17 +222,17 @@ __device__ __forceinline__ void conv1u_issuer(const TcParams& P, unsigned char* 
     for (int lq = wg;; lq += 2, sd++) {
         if ((int)(blockIdx.x + (lq >> 1) * gridDim.x) >= nPairs) break;
         for (int h = 4; h < N::H; h++) {
-            const int oh = h - 4, gd = sd * N::OH1 + oh, b = gd & 1;
+            const int oh = h - 4, gd = sd * N::OH1 + oh, b = gd & (U::ND - 1);
             const int Rg = sd * N::H + h;
-            mbar_wait(&a_full[Rg % 6], (Rg / 6) & 1);         // row h is in TMEM (rows before it were waited for earlier)
-            mbar_wait(&d_empty[b], ((gd >> 1) & 1) ^ 1);      // the previous tenant of this D buffer has been read
+            mbar_wait(&a_full[Rg & (U::NA - 1)], (Rg / U::NA) & 1);  // row h is in TMEM (arrivals are in row order)
+            mbar_wait(&d_empty[b], ((gd / U::ND) & 1) ^ 1);          // the previous tenant of this D buffer has been read
             tc5_fence_after();
             if (elect_one()) {
 #pragma unroll
                 for (int t = 0; t < 2; t++)
 #pragma unroll
                     for (int kh = 0; kh < 5; kh++) {
-                        const int slot = (Rg - 4 + kh) % 6;
+                        const int slot = (Rg - 4 + kh) & (U::NA - 1);
                         umma_ts(tm + U::TM_D + b * 32 + t * 16, tm + U::TM_A + slot * 16 + t * 8,
                                 umma_bdesc(b_base + (t * 5 + kh) * 512), idesc, kh > 0 ? 1u : 0u);
                     }
