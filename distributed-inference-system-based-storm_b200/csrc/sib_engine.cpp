@@ -348,6 +348,17 @@ extern "C" int sib_model_describe(const void* blob, size_t n, sib_model_info* ou
     return SIB_OK;
 }
 
+extern "C" long sib_model_import_pb(const void* pb, size_t n, void* out, size_t cap) {
+    std::vector<uint8_t> blob;
+    std::string err;
+    const int r = import_pb(pb, n, &blob, &err);
+    if (r) { set_error(err); return r; }
+    if (!out) return (long)blob.size();
+    if (cap < blob.size()) { set_error("sib_model_import_pb: output buffer too small"); return SIB_ECAP; }
+    std::memcpy(out, blob.data(), blob.size());
+    return (long)blob.size();
+}
+
 extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucfg, sib_engine** out) {
     if (!out) return SIB_EINVAL;
     *out = nullptr;

@@ -29,7 +29,9 @@ struct ModelDesc {
     int preset = -1;  // 0 mnist-lenet5, 1 cifar-lenet5, 2 mnist-wide, 3 cifar-wide, -1 = other shape
 };
 
-int parse_model(const void* blob, size_t n, ModelDesc* out, std::string* err);
+int parse_model(const void* blob, size_t n, ModelDesc* out, std::string* err);  // blob, or saved_model.pb bytes
+// TensorFlow SavedModel / frozen GraphDef bytes -> model blob (sib_pbimport.cpp)
+int import_pb(const void* bytes, size_t n, std::vector<uint8_t>* blob, std::string* err);
 
 void set_error(const std::string& s);
 

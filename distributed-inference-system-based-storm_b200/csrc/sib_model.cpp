@@ -19,8 +19,17 @@ int parse_model(const void* blob, size_t n, ModelDesc* m, std::string* err) {
         return SIB_EINVAL;
     };
     if (!blob || n < 32) return fail("too short");
+    if (std::memcmp(blob, "SIBM", 4) != 0) {
+        // not a blob: the reference's own artefact, model/saved_model.pb (InferenceBolt.java:49), is accepted as is
+        std::vector<uint8_t> converted;
+        std::string ierr;
+        if (import_pb(blob, n, &converted, &ierr) != SIB_OK) {
+            if (err) *err = "model: bad magic, neither a SIBM blob nor an importable saved_model.pb (" + ierr + ")";
+            return SIB_EINVAL;
+        }
+        return parse_model(converted.data(), converted.size(), m, err);
+    }
     const uint32_t* w = static_cast<const uint32_t*>(blob);
-    if (std::memcmp(blob, "SIBM", 4) != 0) return fail("bad magic");
     if (w[1] != 1) return fail("unsupported version");
     *m = ModelDesc{};
     m->in_h = w[2]; m->in_w = w[3]; m->in_c = w[4]; m->n_layers = w[5]; m->n_weights = w[6];

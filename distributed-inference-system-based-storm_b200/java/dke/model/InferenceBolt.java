@@ -36,12 +36,15 @@ public class InferenceBolt extends BaseRichBolt {
         this.collector = outputCollector;
         this.fifo = new ArrayDeque<>();
         byte[] blob;
-        try (InputStream in = getClass().getClassLoader().getResourceAsStream("model/model.sib")) {  // where saved_model.pb lived
+        // model/model.sib if the jar has one, else the reference's own model/saved_model.pb (frozen): the native side takes either
+        ClassLoader cl = getClass().getClassLoader();
+        String res = cl.getResource("model/model.sib") != null ? "model/model.sib" : "model/saved_model.pb";
+        try (InputStream in = cl.getResourceAsStream(res)) {
             ByteArrayOutputStream bo = new ByteArrayOutputStream();
             byte[] buf = new byte[1 << 16];
             for (int n; (n = in.read(buf)) > 0; ) bo.write(buf, 0, n);
             blob = bo.toByteArray();
-        } catch (Exception e) { throw new RuntimeException("model/model.sib missing from the jar", e); }
+        } catch (Exception e) { throw new RuntimeException("neither model/model.sib nor model/saved_model.pb in the jar", e); }
         String p = String.valueOf(map.getOrDefault("sib.precision", "fp16"));
         int prec = p.equals("fp32") ? 2 : p.equals("bf16") ? 1 : 0;
         int[] cfg = { conf(map, "sib.device", -1), ctx.getThisTaskIndex(), conf(map, "sib.max.batch", 0),

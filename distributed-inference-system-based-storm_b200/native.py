@@ -50,6 +50,7 @@ class ModelInfo(C.Structure):
 SYMBOLS = {
     "sib_device_count": (C.c_int, []),
     "sib_model_describe": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(ModelInfo)]),
+    "sib_model_import_pb": (C.c_long, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "sib_engine_open": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "sib_engine_close": (C.c_int, [C.c_void_p]),
     "sib_engine_info": (C.c_int, [C.c_void_p, C.POINTER(ModelInfo), C.POINTER(Config)]),
@@ -102,6 +103,18 @@ def describe(blob: bytes) -> ModelInfo:
     if rc:
         raise SibError(rc, "sib_model_describe")
     return info
+
+
+def import_pb(saved_model_pb: bytes) -> bytes:
+    """TensorFlow SavedModel / frozen GraphDef bytes (the reference's model/saved_model.pb) -> model blob."""
+    need = lib.sib_model_import_pb(saved_model_pb, len(saved_model_pb), None, 0)
+    if need < 0:
+        raise SibError(int(need), "sib_model_import_pb")
+    buf = C.create_string_buffer(need)
+    got = lib.sib_model_import_pb(saved_model_pb, len(saved_model_pb), buf, need)
+    if got != need:
+        raise SibError(int(got), "sib_model_import_pb")
+    return buf.raw
 
 
 def json_decode(text: bytes, cap: int | None = None):

@@ -90,6 +90,13 @@ typedef struct sib_model_info {
 /* ---- life cycle: replaces InferenceBolt.prepare()'s SavedModelBundle.load / session (InferenceBolt.java:43-62) */
 int sib_device_count(void);
 int sib_model_describe(const void *model_blob, size_t n, sib_model_info *out);
+/* Everywhere a model blob is taken, the reference's own artefact -- the bytes of model/saved_model.pb, a TensorFlow
+ * SavedModel (or frozen GraphDef) with constant weights, InferenceBolt.java:49-58 -- is accepted as well and
+ * converted on the fly. This call exposes the conversion: writes the blob into out (capacity cap) and returns its
+ * length; out == NULL returns the length needed; SIB_ECAP if cap is too small; SIB_EINVAL (text in
+ * sib_last_error) if the graph is not Placeholder -> [Conv2D VALID s1 + BiasAdd + Relu + MaxPool 2x2/2]* ->
+ * Reshape -> [MatMul + BiasAdd (+ Relu)]* -> Softmax with frozen weights. Replaces SavedModelBundle.load (:57). */
+long sib_model_import_pb(const void *saved_model_pb, size_t n, void *out, size_t cap);
 int sib_engine_open(const void *model_blob, size_t n, const sib_config *cfg, sib_engine **out);
 int sib_engine_close(sib_engine *e); /* flushes, waits for in-flight batches, frees everything */
 int sib_engine_info(sib_engine *e, sib_model_info *out, sib_config *effective_cfg);
