@@ -18,10 +18,17 @@ __device__ __forceinline__ void cp_async16(float* smem_dst, const float* gmem_sr
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-constexpr int kGT = 256;
-constexpr int kGI = 5;  // images per CTA pass: the dense weights stream from L2 once per 5 images, and 5 images give
-                        // 980 conv1 / 500 conv2 work items = 3.83 / 1.95 rounds of the 256 threads (4 images left a
-                        // quarter of the last conv1 round and half of the last conv2 round idle: r01 guard profile)
+// One CTA per SM, 24 warps, up to 10 listed images per pass. A 65 536-image batch lists ~1 000-1 400 images, i.e.
+// 6-10 per SM: that is 1 250-1 850 conv1 work items, 2-3 rounds of 768 threads. (256-thread CTAs, two per SM, with
+// 3-5 images each needed 3-4 conv1 rounds and 2 conv2 rounds for the same images: r01 guard profiles.)
+#ifndef SIB_GUARD_THREADS
+#define SIB_GUARD_THREADS 768
+#endif
+#ifndef SIB_GUARD_IMGS
+#define SIB_GUARD_IMGS 10
+#endif
+constexpr int kGT = SIB_GUARD_THREADS;
+constexpr int kGI = SIB_GUARD_IMGS;  // images per CTA pass (shared-memory bound: 10 cifar images + scratch = 206 KB)
 
 template <int H_, int W_, int C_>
 struct GNet {
@@ -30,10 +37,12 @@ struct GNet {
     static constexpr int C1 = 6, C2 = 16, F1 = 120, F2 = 84, F3 = 10;
     static constexpr int IMG = H * W * C, P1 = PH1 * PW1 * C1, FEAT = PH2 * PW2 * C2;
     static constexpr int NW1 = 25 * C * C1, NW2 = 25 * C1 * C2;
-    static constexpr int KSL = 8;  // k slices of fc1
-    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && 3 * F2 <= kGT && kGI * 32 <= kGT && F2 % 3 == 0, "mapping");
+    // dense stages: as many k slices as the threads allow, so that the per-thread chain of L2 weight loads is short
+    static constexpr int KSL = kGT >= 600 ? FEAT / (FEAT % 20 == 0 ? 20 : 16) : 8;  // k slices of fc1 (x 30 float4 columns)
+    static constexpr int S2 = kGT >= 8 * F2 ? 8 : 3, K2 = F1 / S2;                   // k slices of fc2 (x 84 outputs)
+    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && S2 * F2 <= kGT && kGI * 32 <= kGT && F2 % 3 == 0 && F1 % S2 == 0, "mapping");
     // shared memory (floats). The images are dead once conv1 has run: the dense stages' scratch overlays them.
-    static constexpr int DENSE = kGI * KSL * F1 + kGI * F1 + kGI * 3 * F2;
+    static constexpr int DENSE = kGI * KSL * F1 + kGI * F1 + kGI * S2 * F2;
     static constexpr int S_IMG = 0, S_PART = 0, S_H1 = S_PART + kGI * KSL * F1, S_H2 = S_H1 + kGI * F1,
                          S_W1 = ((kGI * IMG > DENSE ? kGI * IMG : DENSE) + 3) / 4 * 4, S_P1 = S_W1 + ((NW1 + C1 + 3) / 4) * 4,
                          S_W2 = S_P1 + kGI * P1, S_P2 = S_W2 + NW2 + C2, S_W3 = S_P2 + kGI * FEAT,
@@ -57,8 +66,8 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
     const float* W = m.weights;
     const DeviceLayer L0 = m.layer[0], L1 = m.layer[1], L2 = m.layer[2], L3 = m.layer[3], L4 = m.layer[4];
     auto load_images = [&](int it, int imgs) {  // asynchronous copies: nothing waits until cp_async_wait_all()
-        for (int g = 0; g < kGI; g++) {          // rows past the end of the share repeat its last image (results dropped)
-            const int img = list[it + min(g, imgs - 1)];
+        for (int g = 0; g < imgs; g++) {
+            const int img = list[it + g];
             const float* src = in + (size_t)img * G::IMG;
             float* dst = sm + G::S_IMG + g * G::IMG;
             for (int i = tid; i < G::IMG / 4; i += kGT) cp_async16(dst + 4 * i, src + 4 * i);
@@ -83,7 +92,7 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
         cp_async_wait_all();
         __syncthreads();
         // ---- conv1 + bias + ReLU + pool: item = (image, pooled position); 2x2 positions x 6 channels in registers
-        for (int item = tid; item < kGI * G::PH1 * G::PW1; item += kGT) {
+        for (int item = tid; item < imgs * G::PH1 * G::PW1; item += kGT) {
             const int g = item / (G::PH1 * G::PW1), pp = item % (G::PH1 * G::PW1);
             const int py = pp / G::PW1, px = pp % G::PW1;
             float acc[2][2][G::C1];
@@ -125,7 +134,7 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
         }
         __syncthreads();
         // ---- conv2 + bias + ReLU + pool: item = (image, pooled position, 4 output channels)
-        for (int item = tid; item < kGI * G::PH2 * G::PW2 * 4; item += kGT) {
+        for (int item = tid; item < imgs * G::PH2 * G::PW2 * 4; item += kGT) {
             const int q = item & 3, t2 = item >> 2;
             const int g = t2 / (G::PH2 * G::PW2), pos = t2 % (G::PH2 * G::PW2);
             const int py = pos / G::PW2, px = pos % G::PW2;
@@ -166,7 +175,8 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             }
         }
         __syncthreads();
-        // ---- fc1: 8 k-slices x 30 float4 columns; each 128-bit weight load from L2 serves all the images of the pass
+        // ---- fc1: KSL k-slices x 30 float4 columns; each 128-bit weight load from L2 serves all the images of the pass
+        // (rows of images past `imgs` hold stale data; their results are never read)
         if (tid < G::KSL * (G::F1 / 4)) {
             const int n4 = tid % (G::F1 / 4), ks = tid / (G::F1 / 4);
             constexpr int KL = G::FEAT / G::KSL;
@@ -198,27 +208,28 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);
         }
         __syncthreads();
-        // ---- fc2: 3 k-slices x 84 outputs, one weight load per k for all the images of the pass
-        if (tid < 3 * G::F2) {
+        // ---- fc2: S2 k-slices x 84 outputs, one weight load per k for all the images of the pass
+        if (tid < G::S2 * G::F2) {
             const int j = tid % G::F2, ks = tid / G::F2;
-            const float* wp = W + L3.w_off + (size_t)(ks * 40) * G::F2 + j;
+            const float* wp = W + L3.w_off + (size_t)(ks * G::K2) * G::F2 + j;
             float a[kGI];
 #pragma unroll
             for (int g = 0; g < kGI; g++) a[g] = 0.f;
-#pragma unroll 8
-            for (int k = 0; k < 40; k++) {
+#pragma unroll 5
+            for (int k = 0; k < G::K2; k++) {
                 const float w = __ldg(wp + (size_t)k * G::F2);
 #pragma unroll
-                for (int g = 0; g < kGI; g++) a[g] = fmaf(sm[G::S_H1 + g * G::F1 + ks * 40 + k], w, a[g]);
+                for (int g = 0; g < kGI; g++) a[g] = fmaf(sm[G::S_H1 + g * G::F1 + ks * G::K2 + k], w, a[g]);
             }
 #pragma unroll
-            for (int g = 0; g < kGI; g++) sm[G::S_H2 + (g * 3 + ks) * G::F2 + j] = a[g];
+            for (int g = 0; g < kGI; g++) sm[G::S_H2 + (g * G::S2 + ks) * G::F2 + j] = a[g];
         }
         __syncthreads();
         for (int o = tid; o < kGI * G::F2; o += kGT) {
             const int g = o / G::F2, j = o % G::F2;
-            const float v = sm[G::S_H2 + (g * 3) * G::F2 + j] + sm[G::S_H2 + (g * 3 + 1) * G::F2 + j] +
-                            sm[G::S_H2 + (g * 3 + 2) * G::F2 + j] + __ldg(W + L3.b_off + j);
+            float v = __ldg(W + L3.b_off + j);
+#pragma unroll
+            for (int ks = 0; ks < G::S2; ks++) v += sm[G::S_H2 + (g * G::S2 + ks) * G::F2 + j];
             sm[G::S_H1 + g * G::F1 + j] = fmaxf(v, 0.f);  // h2 reuses the h1 area (fc2 has finished reading it)
         }
         __syncthreads();
@@ -261,17 +272,20 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 template <typename G>
 int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected, const int32_t* d_list,
                  const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, cudaStream_t st) {
-    static bool configured[64] = {};
+    static int ctas_per_sm[64] = {};
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     const int smem = G::S_TOTAL * (int)sizeof(float);
-    if (!configured[dev & 63]) {
+    if (!ctas_per_sm[dev & 63]) {
         cudaError_t e = cudaFuncSetAttribute(guard_fp32_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return (int)e;
-        configured[dev & 63] = true;
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, guard_fp32_kernel<G>, kGT, smem);
+        if (e != cudaSuccess) return (int)e;
+        ctas_per_sm[dev & 63] = occ > 0 ? occ : 1;
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = max(1, min((expected + kGI - 1) / kGI, sms * 2));
+    const int grid = max(1, min(expected, sms * ctas_per_sm[dev & 63]));  // one wave; a CTA's share may take several passes
     guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, d_list, d_count, cap, d_probs, d_logits, d_argmax);
     return (int)cudaGetLastError();
 }
