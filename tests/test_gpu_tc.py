@@ -134,6 +134,25 @@ def test_tc_full_size_properties(sib, presets):
     assert np.abs(l4 - lf).max() <= 5e-2
 
 
+def test_near_tie_policy(sib, oracle, presets):
+    """Image 713334 of the mnist D2 stream (batch 10, offset 57974) is the one argmax difference against the fp32 oracle
+    in 2^20 images (tools/batch_sweep.py, profiles/batch_sweep_r01.jsonl): its top-2 fp64 margin is 9.6e-7, below the
+    fp32 summation-order noise (the oracle and the GPU fp32 kernels differ by up to 3e-6 on these logits), so two fp32
+    implementations may legitimately disagree. What must hold there: the emitted class is one of the two tied classes,
+    it is the argmax of the guard's own fp32 logits, and those logits are within fp32 noise of the oracle's."""
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 10, 65536)[57974:57975]
+    om = oracle.Model(m.to_blob())
+    l64 = np.asarray(om.forward64(x)[0]).ravel()
+    top2 = np.argsort(l64)[::-1][:2]
+    assert l64[top2[0]] - l64[top2[1]] < 1e-5
+    with sib.native.Engine(m.to_blob(), max_batch=64) as e:      # default precision, guard on
+        p, lg, am = e.forward_sync(np.repeat(x, 16, axis=0))
+    assert (am == am[0]).all() and int(am[0]) in top2.tolist()
+    assert int(am[0]) == int(lg[0].argmax())
+    assert np.abs(lg[0] - l64).max() < 2e-5
+
+
 def test_engine_micro_batches_on_tc_path(sib, oracle, presets):
     m = presets["mnist-lenet5"]
     x = sib.modelspec.synthetic_images(m, 66, 200)
