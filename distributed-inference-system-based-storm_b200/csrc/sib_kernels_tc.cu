@@ -62,7 +62,10 @@ constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two ba
 #define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
-constexpr int kFcWarps = 1;
+#ifndef SIB_FC_IN_CONV2
+#define SIB_FC_IN_CONV2 0   // 1: no fc warp; conv2 warp (pair % kConv2Warps) runs the dense head of a pair after its tiles
+#endif
+constexpr int kFcWarps = SIB_FC_IN_CONV2 ? 0 : 1;
 constexpr int kIssueWarps = SIB_CONV1_UMMA ? 2 : 0;  // tcgen05.mma issuers (conv1 warps = two teams of 4)
 constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps + kIssueWarps;
 constexpr int kThreadsTc = kWarps * 32;
@@ -117,8 +120,9 @@ struct Net {
     static constexpr int S_P1 = SIB_CONV1_UMMA ? S_B1U + 2 * 5 * 512 : S_BIAS + 264 * 4;
     static constexpr int S_P2 = S_P1 + NB1 * P1_BUF * 2;
     static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
-    static constexpr int S_H2 = S_H1 + kPair * H1_STRIDE * 2;
-    static constexpr int S_RING = S_H2 + kPair * H2_STRIDE * 2;
+    static constexpr int NHB = SIB_FC_IN_CONV2 ? 2 : 1;                    // h1/h2 buffers: dense heads of two pairs may overlap
+    static constexpr int S_H2 = S_H1 + NHB * kPair * H1_STRIDE * 2;
+    static constexpr int S_RING = S_H2 + NHB * kPair * H2_STRIDE * 2;
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
     static constexpr int URING_ROW = 2 * W * C + 16;                       // halves: Umma<N>::UROW
     static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * (SIB_CONV1_UMMA ? URING_ROW : RING_ROW) * 2; // cp.async landing zone
@@ -412,6 +416,9 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
 // ---- conv2 role ---------------------------------------------------------------------------------------------
 
 template <typename N, typename T, bool DBG>
+__device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, int lane, int Qi);  // below
+
+template <typename N, typename T, bool DBG>
 __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* smem, int w2, int lane) {
     const int g = lane >> 2, t = lane & 3;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
@@ -420,15 +427,18 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
     uint64_t* p2_full = bars + N::B_P2F;
     uint64_t* p2_empty = bars + N::B_P2E;
     uint32_t bW[5][2][2][2];  // [kh][k step][n tile][reg]: the whole 150x16 filter, register-resident
+    auto load_filter = [&]() {
 #pragma unroll
-    for (int kh = 0; kh < 5; kh++)
+        for (int kh = 0; kh < 5; kh++)
 #pragma unroll
-        for (int ks = 0; ks < 2; ks++)
+            for (int ks = 0; ks < 2; ks++)
 #pragma unroll
-            for (int nt = 0; nt < 2; nt++) {
-                const uint2 v = *reinterpret_cast<const uint2*>(P.wpack + N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64 + lane * 2);
-                bW[kh][ks][nt][0] = v.x; bW[kh][ks][nt][1] = v.y;
-            }
+                for (int nt = 0; nt < 2; nt++) {
+                    const uint2 v = *reinterpret_cast<const uint2*>(P.wpack + N::W_C2 + ((kh * 2 + ks) * 2 + nt) * 64 + lane * 2);
+                    bW[kh][ks][nt][0] = v.x; bW[kh][ks][nt][1] = v.y;
+                }
+    };
+    load_filter();
     const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS) + 8;
     const float bias00 = biasp[2 * t], bias01 = biasp[2 * t + 1], bias10 = biasp[8 + 2 * t], bias11 = biasp[8 + 2 * t + 1];
     const int nPairs = (P.n + kPair - 1) / kPair;
@@ -502,13 +512,24 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
         }
         mbar_arrive(&p1_empty[buf1]);
         mbar_arrive(&p2_full[buf2]);
+#if SIB_FC_IN_CONV2
+        {   // was that this warp's last tile of pair Qi? then warp (Qi % kConv2Warps) runs the pair's dense head
+            static_assert(2 * N::TILES2 >= 2 * kConv2Warps, "every conv2 warp has tiles in every pair");
+            const int nQi = ((gi + kConv2Warps) / N::TILES2) >> 1;
+            if ((nQi != Qi || (int)(blockIdx.x + nQi * gridDim.x) >= nPairs) && Qi % kConv2Warps == w2) {
+                fc_pair<N, T, DBG>(P, smem, lane, Qi);
+                load_filter();  // the filter registers were free for the dense head's accumulators
+            }
+        }
+#endif
     }
 }
 
 // ---- fc role (one warp) -------------------------------------------------------------------------------------
 
+// the dense head of pair Qi (16 images): p2[Qi & 1] -> probabilities, argmax, margin
 template <typename N, typename T, bool DBG>
-__device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, int lane) {
+__device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, int lane, int Qi) {
     const int g = lane >> 2, t = lane & 3;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
     uint64_t* p2_full = bars + N::B_P2F;
@@ -517,13 +538,10 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
     const uint32_t* w2 = w1 + (N::W_F2 - N::W_F1);
     const uint32_t* w3 = w1 + (N::W_F3 - N::W_F1);
     const float* bias = reinterpret_cast<const float*>(smem + N::S_BIAS);  // c1[8] c2[16] f1[128] f2[96] f3[16]
-    uint16_t* h1 = reinterpret_cast<uint16_t*>(smem + N::S_H1);
-    uint16_t* h2 = reinterpret_cast<uint16_t*>(smem + N::S_H2);
-    const int nPairs = (P.n + kPair - 1) / kPair;
-
-    for (int Qi = 0;; Qi++) {
+    uint16_t* h1 = reinterpret_cast<uint16_t*>(smem + N::S_H1) + (Qi % N::NHB) * kPair * N::H1_STRIDE;
+    uint16_t* h2 = reinterpret_cast<uint16_t*>(smem + N::S_H2) + (Qi % N::NHB) * kPair * N::H2_STRIDE;
+    {
         const int pair = blockIdx.x + Qi * gridDim.x;
-        if (pair >= nPairs) break;
         const int buf = Qi & 1, use = Qi >> 1;
         const uint16_t* p2 = reinterpret_cast<const uint16_t*>(smem + N::S_P2) + buf * N::P2_BUF;
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
@@ -665,6 +683,13 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
     }
 }
 
+// ---- fc role (one warp): every pair's dense head ----------------------------------------------------------------------
+template <typename N, typename T, bool DBG>
+__device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, int lane) {
+    const int nPairs = (P.n + kPair - 1) / kPair;
+    for (int Qi = 0; (int)(blockIdx.x + Qi * gridDim.x) < nPairs; Qi++) fc_pair<N, T, DBG>(P, smem, lane, Qi);
+}
+
 template <typename N, typename T, bool DBG>
 __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -701,7 +726,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
             }
             for (int i = 0; i < 2; i++) {
                 mbar_init(&bars[N::B_P2F + i], 2 * N::TILES2 * 32);   // p2_full : two slots of conv2 tiles
-                mbar_init(&bars[N::B_P2E + i], kFcWarps * 32);        // p2_empty: every fc lane
+                mbar_init(&bars[N::B_P2E + i], 32);                   // p2_empty: every lane of the warp that runs the pair's dense head
             }
         }
     }
@@ -722,7 +747,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     __syncthreads();
     if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
     else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
-    else fc_role<N, T, DBG>(P, smem, lane);
+    else if (kFcWarps) fc_role<N, T, DBG>(P, smem, lane);
 #endif
 }
 
