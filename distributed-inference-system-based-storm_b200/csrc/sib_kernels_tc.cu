@@ -62,6 +62,9 @@ constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two ba
 #define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
+#ifndef SIB_TAIL_FIRST
+#define SIB_TAIL_FIRST 0     // 1: conv2 and fc warps get the lowest warp ids (they are the oldest warps of their sub-partition)
+#endif
 #ifndef SIB_FC_IN_CONV2
 #define SIB_FC_IN_CONV2 0   // 1: no fc warp; conv2 warp (pair % kConv2Warps) runs the dense head of a pair after its tiles
 #endif
@@ -745,8 +748,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     if (warp == 0) tmem_free_all(tmem);
 #else
     __syncthreads();
-    if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
-    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
+    // role of hardware warp `warp`: with SIB_TAIL_FIRST the conv2 / fc warps take the lowest warp ids (sub-partition
+    // placement is unchanged: ids differ by a multiple of 4)
+    const int rw = SIB_TAIL_FIRST ? (warp + kConv1Warps) % kWarps : warp;
+    if (rw < kConv1Warps) conv1_role<N, T, DBG>(P, smem, rw, lane);
+    else if (rw < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, rw - kConv1Warps, lane);
     else if (kFcWarps) fc_role<N, T, DBG>(P, smem, lane);
 #endif
 }
