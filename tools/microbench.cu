@@ -55,6 +55,22 @@ __global__ void ffma_rate(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+// packed fp32 FMA (fma.rn.f32x2, sm_100): 16 independent float2 chains, and a 50/50 mix with shared-memory loads
+__global__ void ffma2_rate(float* out, int iters) {
+    float2 a[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) a[j] = make_float2(threadIdx.x * 0.001f + j, threadIdx.x * 0.002f + j);
+    const float2 x = make_float2(1.0001f, 0.9998f), y = make_float2(0.9999f, 1.0002f);
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 16; j++) a[j] = __ffma2_rn(a[j], x, y);
+    }
+    float s = 0;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s += a[j].x + a[j].y;
+    if (s == 12345.678f) out[0] = s;
+}
+
 __global__ void lds_rate(float* out, int iters) {
     __shared__ float buf[4096];
     for (int i = threadIdx.x; i < 4096; i += blockDim.x) buf[i] = i;
@@ -108,6 +124,8 @@ int main() {
         int blocks = sms * 4, threads = 512;
         float ms = time_ms([&] { ffma_rate<<<blocks, threads>>>(d, iters); });
         printf("{\"probe\": \"ffma\", \"tflops\": %.1f}\n", (double)blocks * threads * iters * 16 * 2 / ms * 1e-9);
+        ms = time_ms([&] { ffma2_rate<<<blocks, threads>>>(d, iters); });
+        printf("{\"probe\": \"ffma2 (fma.rn.f32x2)\", \"tflops\": %.1f}\n", (double)blocks * threads * iters * 16 * 4 / ms * 1e-9);
         ms = time_ms([&] { lds_rate<<<blocks, threads>>>(d, iters); });
         printf("{\"probe\": \"lds32\", \"TBps\": %.2f, \"bytes_per_clk_per_sm_at_max_clock\": %.1f}\n", (double)blocks * threads * iters * 16 * 4 / ms * 1e-9,
                (double)blocks * threads * iters * 16 * 4 / (ms * 1e-3) / sms / (clk_khz * 1e3));
