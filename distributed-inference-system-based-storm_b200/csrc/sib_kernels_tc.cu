@@ -739,10 +739,13 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     tc5_fence_after();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + N::S_TMEM);
     static_assert(kConv1Warps == 8, "tcgen05 conv1: two teams of 4 warps (one warp per TMEM lane quadrant)");
-    if (warp < 8) conv1u_worker<N, T, DBG>(P, smem, warp >> 2, warp & 3, lane, tmem);
-    else if (warp < kConv1Warps + kConv2Warps) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane);
-    else if (warp < kConv1Warps + kConv2Warps + kFcWarps) fc_role<N, T, DBG>(P, smem, lane);
-    else conv1u_issuer<N, T>(P, smem, warp - kConv1Warps - kConv2Warps - kFcWarps, tmem);
+#ifndef SIB_ROLE_MASK
+#define SIB_ROLE_MASK 15   // diagnostic: compile only some roles (1 worker, 2 conv2, 4 fc, 8 issuer) to read their register needs
+#endif
+    if (warp < 8) { if (SIB_ROLE_MASK & 1) conv1u_worker<N, T, DBG>(P, smem, warp >> 2, warp & 3, lane, tmem); }
+    else if (warp < kConv1Warps + kConv2Warps) { if (SIB_ROLE_MASK & 2) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane); }
+    else if (warp < kConv1Warps + kConv2Warps + kFcWarps) { if (SIB_ROLE_MASK & 4) fc_role<N, T, DBG>(P, smem, lane); }
+    else if (SIB_ROLE_MASK & 8) conv1u_issuer<N, T>(P, smem, warp - kConv1Warps - kConv2Warps - kFcWarps, tmem);
     tc5_fence_before();
     __syncthreads();
     if (warp == 0) tmem_free_all(tmem);
