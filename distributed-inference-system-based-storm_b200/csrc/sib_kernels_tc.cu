@@ -62,6 +62,12 @@ constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two ba
 #define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
+#ifndef SIB_BIAS_IN_ACC1
+#define SIB_BIAS_IN_ACC1 0     // conv1 / conv2 accumulators start at the bias instead of adding it after the pool
+#endif
+#ifndef SIB_BIAS_IN_ACC2
+#define SIB_BIAS_IN_ACC2 0
+#endif
 #ifndef SIB_TAIL_FIRST
 #define SIB_TAIL_FIRST 0     // 1: conv2 and fc warps get the lowest warp ids (they are the oldest warps of their sub-partition)
 #endif
@@ -370,7 +376,10 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
 #pragma unroll
         for (int h = 0; h < N::H; h++) {
             if (h + 1 < N::H) stage_row(h + 1);
-            float cE[4] = {0.f, 0.f, 0.f, 0.f}, cO[4] = {0.f, 0.f, 0.f, 0.f};
+            // the accumulators start at the bias (same for the 4 positions of a pool window, so max(.) + b == max(. + b))
+            float cE[4], cO[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) cE[i] = cO[i] = SIB_BIAS_IN_ACC1 ? ((i & 1) ? bias1 : bias0) : 0.f;
             float dE[4] = {0.f, 0.f, 0.f, 0.f}, dO[4] = {0.f, 0.f, 0.f, 0.f};
             if (h >= 4) {
                 const int oh = h - 4;
@@ -386,15 +395,19 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
                 const int oh = h - 4;
                 float m[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) m[i] = fmaxf(cE[i] + dE[i], cO[i] + dO[i]);  // pool over the column pair
+                for (int i = 0; i < 4; i++)  // pool over the column pair (x + 0.f is not a no-op to the compiler: no dead adds)
+                    m[i] = SIB_SPLIT_ACC ? fmaxf(cE[i] + dE[i], cO[i] + dO[i]) : fmaxf(cE[i], cO[i]);
                 if ((oh & 1) == 0) {
 #pragma unroll
                     for (int i = 0; i < 4; i++) prev[i] = m[i];
                 } else {
                     const int ph = oh >> 1;
                     // relu(max(.)+b) == max over the window of relu(.+b)
-                    const float v0 = fmaxf(fmaxf(m[0], prev[0]) + bias0, 0.f), v1 = fmaxf(fmaxf(m[1], prev[1]) + bias1, 0.f);
-                    const float v2 = fmaxf(fmaxf(m[2], prev[2]) + bias0, 0.f), v3 = fmaxf(fmaxf(m[3], prev[3]) + bias1, 0.f);
+                    const float pb0 = SIB_BIAS_IN_ACC1 ? 0.f : bias0, pb1 = SIB_BIAS_IN_ACC1 ? 0.f : bias1;
+                    const float v0 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[0], prev[0]), 0.f) : fmaxf(fmaxf(m[0], prev[0]) + pb0, 0.f);
+                    const float v1 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[1], prev[1]), 0.f) : fmaxf(fmaxf(m[1], prev[1]) + pb1, 0.f);
+                    const float v2 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[2], prev[2]), 0.f) : fmaxf(fmaxf(m[2], prev[2]) + pb0, 0.f);
+                    const float v3 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[3], prev[3]), 0.f) : fmaxf(fmaxf(m[3], prev[3]) + pb1, 0.f);
                     if (t < 3) {
                         *reinterpret_cast<uint32_t*>(p1 + o0 + ph * N::P1_ROW) = Ops<T>::pack(v0, v1);
                         *reinterpret_cast<uint32_t*>(p1 + o1 + ph * N::P1_ROW) = Ops<T>::pack(v2, v3);
@@ -485,8 +498,12 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
             load_frags(r);  // consumed by the kh=4 mma at the end of this iteration's chains
             const int oh = r - 4;
             // 4 independent accumulator chains: (n tile) x (k step)
-            float c0[4] = {0.f, 0.f, 0.f, 0.f}, d0[4] = {0.f, 0.f, 0.f, 0.f};
-            float c1[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+            float c0[4], c1[4], d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int i = 0; i < 4; i++) {  // SIB_BIAS_IN_ACC2: the bias rides in the accumulator
+                c0[i] = SIB_BIAS_IN_ACC2 ? ((i & 1) ? bias01 : bias00) : 0.f;
+                c1[i] = SIB_BIAS_IN_ACC2 ? ((i & 1) ? bias11 : bias10) : 0.f;
+            }
 #pragma unroll
             for (int kh = 0; kh < 5; kh++) {
                 Ops<T>::mma(c0, a[(oh + kh) % 5][0], bW[kh][0][0]);
@@ -502,8 +519,10 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
                 for (int i = 0; i < 4; i++) prev[i] = h[i];
             } else {
                 const int ph = oh >> 1;
-                const float v0 = fmaxf(fmaxf(h[0], prev[0]) + bias00, 0.f), v1 = fmaxf(fmaxf(h[1], prev[1]) + bias01, 0.f);
-                const float v2 = fmaxf(fmaxf(h[2], prev[2]) + bias10, 0.f), v3 = fmaxf(fmaxf(h[3], prev[3]) + bias11, 0.f);
+                const float v0 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[0], prev[0]), 0.f) : fmaxf(fmaxf(h[0], prev[0]) + bias00, 0.f);
+                const float v1 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[1], prev[1]), 0.f) : fmaxf(fmaxf(h[1], prev[1]) + bias01, 0.f);
+                const float v2 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[2], prev[2]), 0.f) : fmaxf(fmaxf(h[2], prev[2]) + bias10, 0.f);
+                const float v3 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[3], prev[3]), 0.f) : fmaxf(fmaxf(h[3], prev[3]) + bias11, 0.f);
                 uint16_t* dst = p2 + o2 + ph * N::PW2 * N::C2;
                 *reinterpret_cast<uint32_t*>(dst) = Ops<T>::pack(v0, v1);      // channels 2t, 2t+1
                 *reinterpret_cast<uint32_t*>(dst + 8) = Ops<T>::pack(v2, v3);  // channels 8+2t, 9+2t
