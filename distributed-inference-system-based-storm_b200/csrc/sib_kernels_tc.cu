@@ -62,6 +62,9 @@ constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two ba
 #define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
+#ifndef SIB_DYN_SPANS
+#define SIB_DYN_SPANS 0        // 1: conv1 warps claim their spans from a shared counter (measured: 219 vs 228 M img/s dealt round-robin)
+#endif
 #ifndef SIB_BIAS_IN_ACC1
 #define SIB_BIAS_IN_ACC1 0     // conv1 / conv2 accumulators start at the bias instead of adding it after the pool
 #endif
@@ -281,7 +284,15 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
     };
 
     const uint32_t stage = smem_u32(smem + N::S_STAGE) + cw * N::PD * N::STAGE_ROW + chunk * 16;
-    int gs = cw;
+    // SIB_DYN_SPANS: spans are claimed from a CTA-wide counter instead of being dealt round-robin, so the conv1 warps of a
+    // sub-partition whose tensor pipe is less loaded (no conv2 warp there) end up taking more of them
+    uint32_t* span_ctr = reinterpret_cast<uint32_t*>(smem + N::S_TMEM);
+    auto claim = [&]() -> int {
+        int v = 0;
+        if (lane == 0) v = (int)atomicAdd(span_ctr, 1u);
+        return __shfl_sync(0xffffffffu, v, 0);
+    };
+    int gs = SIB_DYN_SPANS ? claim() : cw;
     int img0;
     bool valid;
     span_src(gs, img0, valid);
@@ -308,8 +319,9 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         // next span (for the tail prefetch)
         int n_img0;
         bool n_valid;
-        span_src(gs + kConv1Warps, n_img0, n_valid);
-        const float* n_src = n_valid ? chunk_ptr(n_img0, (gs + kConv1Warps) % N::SPANS) : src;
+        const int n_gs = SIB_DYN_SPANS ? claim() : gs + kConv1Warps;
+        span_src(n_gs, n_img0, n_valid);
+        const float* n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS) : src;
 
         // fragment offsets into a staged row (halves)
         const int p0 = 32 * s;
@@ -422,7 +434,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             }
         }
         mbar_arrive(&p1_full[buf]);
-        gs += kConv1Warps;
+        gs = n_gs;
         valid = n_valid;
         src = n_src;
         img0 = n_img0;
@@ -736,6 +748,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
 #endif
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+            *reinterpret_cast<uint32_t*>(smem + N::S_TMEM) = 0u;  // mma.sync build: the conv1 span counter lives here
 #if SIB_CONV1_UMMA
             for (int i = 0; i < 8; i++) mbar_init(&bars[N::B_UA + i], 128);     // a_full : every thread of the team that owns the pair
             for (int i = 8; i < 16; i++) mbar_init(&bars[N::B_UA + i], 2);      // a_free : one tcgen05.commit per issuer
