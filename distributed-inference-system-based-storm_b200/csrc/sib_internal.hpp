@@ -3,6 +3,8 @@
 #include <cstddef>
 #include <cstdint>
 #include <string>
+#include <atomic>
+#include <mutex>
 #include <vector>
 
 #include "../../include/sib.h"
@@ -39,6 +41,26 @@ void set_error(const std::string& s);
 long json_decode(const char* utf8, size_t len, float* out, long cap, int64_t dims[4]);
 long json_encode(const float* probs, long n, int n_classes, char* buf, size_t cap);
 int float_to_string(float x, char* buf);
+
+// Per-device bookkeeping for cudaFuncAttributeMaxDynamicSharedMemorySize of ONE kernel (one static instance per
+// kernel instantiation). Engines on several host threads launch concurrently: the limit only ever grows, and the
+// attribute call and the record of it happen under one lock, so a launch never finds the limit below what it needs.
+struct SmemLimit {
+    std::atomic<int> have[64];
+    std::mutex mu;
+    SmemLimit() { for (auto& h : have) h.store(-1, std::memory_order_relaxed); }
+    // returns cudaSuccess (0) or the cudaError_t of the attribute call; `set` performs it for `bytes`
+    template <typename Set>
+    int ensure(int device, int bytes, Set set) {
+        std::atomic<int>& h = have[device & 63];
+        if (h.load(std::memory_order_acquire) >= bytes) return 0;
+        std::lock_guard<std::mutex> lk(mu);
+        if (h.load(std::memory_order_relaxed) >= bytes) return 0;
+        const int rc = set(bytes);
+        if (rc == 0) h.store(bytes, std::memory_order_release);
+        return rc;
+    }
+};
 
 // ---- device side (sib_kernels_*.cu)
 struct DeviceLayer {

@@ -205,15 +205,14 @@ template <int kImgs>
 static int launch_inst(const DeviceModel& m, const float* d_in, int n, int expected, const int32_t* d_idx,
                        const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, float* d_margin,
                        cudaStream_t st) {
-    static int configured_for[64] = {};
+    static SmemLimit limit;  // function attributes are per device
     const int smem = (int)(2u * kImgs * m.max_store_act * sizeof(float));
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
-    if (configured_for[dev & 63] < smem) {  // function attributes are per device
-        cudaError_t e = cudaFuncSetAttribute(forward_fp32_kernel<kImgs>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return (int)e;
-        configured_for[dev & 63] = smem;
-    }
+    if (int rc = limit.ensure(dev, smem, [](int b) {
+            return (int)cudaFuncSetAttribute(forward_fp32_kernel<kImgs>, cudaFuncAttributeMaxDynamicSharedMemorySize, b);
+        }))
+        return rc;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int ctas = (expected + kImgs - 1) / kImgs;  // the kernel grid-strides, so fewer CTAs than items is fine
     const int per_sm = max(1, min(8, (227 * 1024) / (smem + 1024)));

@@ -8,6 +8,8 @@
 // Op semantics as in sib_kernels_fp32.cu (TF 1.x Conv2D/BiasAdd/Relu/MaxPool/MatMul/Softmax; InferenceBolt.java:81-85).
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 #include "sib_internal.hpp"
 
 namespace sib {
@@ -272,20 +274,23 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 template <typename G>
 int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected, const int32_t* d_list,
                  const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, cudaStream_t st) {
-    static int ctas_per_sm[64] = {};
+    static SmemLimit limit;                   // function attributes are per device
+    static std::atomic<int> ctas_per_sm[64];  // per device; zero = not asked yet (threads may race, to the same value)
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     const int smem = G::S_TOTAL * (int)sizeof(float);
-    if (!ctas_per_sm[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(guard_fp32_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return (int)e;
+    if (int rc = limit.ensure(dev, smem, [](int b) {
+            return (int)cudaFuncSetAttribute(guard_fp32_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, b);
+        }))
+        return rc;
+    if (!ctas_per_sm[dev & 63].load()) {
         int occ = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, guard_fp32_kernel<G>, kGT, smem);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, guard_fp32_kernel<G>, kGT, smem);
         if (e != cudaSuccess) return (int)e;
-        ctas_per_sm[dev & 63] = occ > 0 ? occ : 1;
+        ctas_per_sm[dev & 63].store(occ > 0 ? occ : 1);
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int grid = max(1, min(expected, sms * ctas_per_sm[dev & 63]));  // one wave; a CTA's share may take several passes
+    const int grid = max(1, min(expected, sms * ctas_per_sm[dev & 63].load()));  // one wave; a CTA's share may take several passes
     guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, d_list, d_count, cap, d_probs, d_logits, d_argmax);
     return (int)cudaGetLastError();
 }

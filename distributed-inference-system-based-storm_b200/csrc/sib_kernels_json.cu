@@ -209,14 +209,13 @@ size_t json_gpu_max_text() { return kMaxText; }
 int launch_json_decode(const char* d_text, const int32_t* d_desc, int n_tuples, float* d_out, int32_t* d_flags, int H,
                        int W, int C, void* stream) {
     if (n_tuples <= 0) return 0;
-    static bool configured[64] = {};
+    static SmemLimit limit;
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!configured[dev & 63]) {
-        cudaError_t e = cudaFuncSetAttribute(json_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxText + 16 + 2 * kMaxElems);
-        if (e != cudaSuccess) return (int)e;
-        configured[dev & 63] = true;
-    }
+    if (int rc = limit.ensure(dev, kMaxText + 16 + 2 * kMaxElems, [](int b) {
+            return (int)cudaFuncSetAttribute(json_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, b);
+        }))
+        return rc;
     json_decode_kernel<<<n_tuples, kJT, kMaxText + 16 + 2 * kMaxElems, (cudaStream_t)stream>>>(
         reinterpret_cast<const unsigned char*>(d_text), d_desc, d_out, d_flags, H, W, C);
     return (int)cudaGetLastError();

@@ -864,14 +864,13 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
 
 template <typename N, typename T, bool DBG>
 int launch_inst(const TcParams& p, cudaStream_t st) {
-    static bool configured[64] = {};
+    static SmemLimit limit;  // function attributes are per device
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
-    if (!configured[dev & 63]) {  // function attributes are per device
-        cudaError_t e = cudaFuncSetAttribute(forward_tc_kernel<N, T, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, N::S_TOTAL);
-        if (e != cudaSuccess) return (int)e;
-        configured[dev & 63] = true;
-    }
+    if (int rc = limit.ensure(dev, N::S_TOTAL, [](int b) {
+            return (int)cudaFuncSetAttribute(forward_tc_kernel<N, T, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, b);
+        }))
+        return rc;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int pairs = (p.n + kPair - 1) / kPair;
     const int grid = pairs < sms ? pairs : sms;

@@ -150,3 +150,38 @@ def test_loadgen_latency_is_bounded_by_deadline_plus_service(sib, presets):
     with sib.native.Engine(m.to_blob(), max_batch=64, deadline_us=300) as e:
         r = sib.native.loadgen(e, [x[i] for i in range(8)], 200000.0, 20000, mode=sib.native.LG_F32, producers=2)
         assert r["completed"] == 20000
+
+
+def test_engines_on_several_threads_with_different_models(sib, presets):
+    """Executors of one worker process each own an engine (InferenceBolt.java:57-58 per executor); models and
+    precisions differ, so kernels with different shared-memory needs are configured and launched concurrently."""
+    import threading
+
+    combos = [("mnist-lenet5", sib.native.PREC_FP32), ("cifar-wide", sib.native.PREC_FP32),
+              ("cifar-lenet5", sib.native.PREC_FP16), ("mnist-wide", sib.native.PREC_FP32),
+              ("cifar-lenet5", sib.native.PREC_FP32), ("mnist-lenet5", sib.native.PREC_FP16)]
+    want = {}
+    for name, prec in combos:  # single-threaded answers first
+        m = presets[name]
+        x = sib.modelspec.synthetic_images(m, 70, 300)
+        with sib.native.Engine(m.to_blob(), precision=prec, max_batch=512) as e:
+            want[(name, prec)] = e.forward_sync(x)[0].copy()
+    errors = []
+
+    def run(name, prec):
+        try:
+            m = presets[name]
+            x = sib.modelspec.synthetic_images(m, 70, 300)
+            for _ in range(3):
+                with sib.native.Engine(m.to_blob(), precision=prec, max_batch=512) as e:
+                    for _ in range(5):
+                        got = e.forward_sync(x)[0]
+                        if got.tobytes() != want[(name, prec)].tobytes():
+                            errors.append((name, prec, float(np.abs(got - want[(name, prec)]).max())))
+        except Exception as ex:  # noqa: BLE001
+            errors.append((name, prec, repr(ex)))
+
+    ts = [threading.Thread(target=run, args=c) for c in combos]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors

@@ -99,6 +99,22 @@ def test_guard_makes_argmax_exact(sib, oracle, presets, name, prec):
     assert np.abs(gl - lg).max() <= tl and np.abs(gp - pr).max() <= tp
 
 
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+@pytest.mark.parametrize("n", [1, 11, 1480, 1481, 5000])
+def test_guard_recomputes_everything_when_asked(sib, oracle, presets, name, n):
+    """tau = 1e9 lists every image: the guard kernel then carries the whole batch (shares of several 10-image passes
+    per CTA, ragged last pass, fewer images than CTAs) and its output must be the fp32 network."""
+    m = presets[name]
+    x = sib.modelspec.synthetic_images(m, 67, n)
+    lg, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), max_batch=max(n, 16), guard=True, guard_tau=1e9) as e:
+        gp, gl, ga = e.forward_sync(x)
+    assert np.abs(gl - lg).max() <= 1e-4 and np.abs(gp - pr).max() <= 1e-5
+    s = np.sort(lg.astype(np.float64), 1)
+    clear = s[:, -1] - s[:, -2] > 1e-4
+    assert (ga[clear] == lg.argmax(1)[clear]).all()
+
+
 @pytest.mark.parametrize("n", [1, 7, 8, 9, 15, 16, 17, 33, 2369])
 def test_tc_batch_edges(sib, oracle, presets, n):
     m = presets["cifar-lenet5"]
