@@ -62,6 +62,12 @@ constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two ba
 #define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
+#ifndef SIB_CONV1_PACK2
+#define SIB_CONV1_PACK2 1
+#endif
+#ifndef SIB_REG_STAGE
+#define SIB_REG_STAGE 1       // 0 forces the cp.async staging ring (kept for heights that are not a multiple of 2 batches)
+#endif
 #ifndef SIB_DYN_SPANS
 #define SIB_DYN_SPANS 0        // 1: conv1 warps claim their spans from a shared counter (measured: 219 vs 228 M img/s dealt round-robin)
 #endif
@@ -93,6 +99,9 @@ struct Net {
     static constexpr int IMG = H * W * C;
     static constexpr int ROWF = W * C;              // floats per image row
     static constexpr int K1ROW = 5 * C;             // real K per kernel row of conv1 (<= 15)
+    // One input channel: a kernel row needs 5 (+1 for the odd-column shift) of the 16 K slots, so two kernel rows share one
+    // mma (k 0..7 = row 2s, k 8..15 = row 2s+1): 3 mma per tile and output row instead of 5, and half the fragment loads.
+    static constexpr bool PACK2 = (C == 1) && SIB_CONV1_PACK2;
     static constexpr int SPANS = kG * OW1 / 32;     // conv1 work items per slot: 32 output columns x all rows
     static constexpr int TILES2 = kG * OW2 / 16;    // conv2 M tiles per slot
     static constexpr int FEAT = PH2 * PW2 * C2;     // 400 | 256
@@ -108,8 +117,8 @@ struct Net {
     static constexpr int H1_STRIDE = 136, H2_STRIDE = 104;
     // Input staging. H % 8 == 0: two register batches of 4 rows (2 scoreboard slots, no shared-memory cost).
     // Otherwise: a cp.async ring of PD rows per warp (in-order groups, costs ~10 shared-memory wavefronts a row).
-    static constexpr bool REG_STAGE = (H % 8 == 0);
-    static constexpr int PD = REG_STAGE ? 8 : 7;                    // rows in flight per conv1 warp
+    static constexpr bool REG_STAGE = (H % (2 * SIB_BATCH_ROWS) == 0) && SIB_REG_STAGE;
+    static constexpr int PD = REG_STAGE ? 2 * SIB_BATCH_ROWS : 7;   // rows in flight per conv1 warp
     static constexpr int NCHUNK = (40 * C + 3) / 4;                 // 16-byte chunks per staged span row
     static constexpr int RING_ROW = ((40 * C + 16 + 7) / 8) * 8;    // halves per staged row incl. zero slack
     static_assert(kG * OW1 % 32 == 0 && kG * OW2 % 16 == 0 && FEAT % 16 == 0 && (SIB_CONV1_UMMA || H % PD == 0) && ((!REG_STAGE && !SIB_CONV1_UMMA) || H % (2 * kBR) == 0), "tiling");
@@ -375,9 +384,14 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             const uint16_t* rr = ring + (r & 1) * N::RING_ROW;
             uint32_t(&e)[4] = aE[r % 5];
             uint32_t(&o)[4] = aO[r % 5];
-            e[0] = lds32(rr + offE0); e[1] = lds32(rr + offE1); e[2] = lds32(rr + offE0 + 8); e[3] = lds32(rr + offE1 + 8);
-            o[0] = lds32(rr + offE0 + kOdd); o[1] = lds32(rr + offE1 + kOdd);
-            o[2] = lds32(rr + offE0 + kOdd + 8); o[3] = lds32(rr + offE1 + kOdd + 8);
+            e[0] = lds32(rr + offE0); e[1] = lds32(rr + offE1);
+            if constexpr (N::PACK2) {  // k 8..15 of a fragment come from the next row's k 0..7; odd tile = even tile (kOdd = 0)
+                e[2] = e[3] = 0u; o[0] = e[0]; o[1] = e[1]; o[2] = o[3] = 0u;
+            } else {
+                e[2] = lds32(rr + offE0 + 8); e[3] = lds32(rr + offE1 + 8);
+                o[0] = lds32(rr + offE0 + kOdd); o[1] = lds32(rr + offE1 + kOdd);
+                o[2] = lds32(rr + offE0 + kOdd + 8); o[3] = lds32(rr + offE1 + kOdd + 8);
+            }
         };
 
         stage_row(0);
@@ -395,12 +409,24 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             float dE[4] = {0.f, 0.f, 0.f, 0.f}, dO[4] = {0.f, 0.f, 0.f, 0.f};
             if (h >= 4) {
                 const int oh = h - 4;
+                if constexpr (N::PACK2) {
+                    // fragment of kernel rows (2s, 2s+1) = k 0..7 of input row oh+2s | k 0..7 of input row oh+2s+1
+#pragma unroll
+                    for (int sp = 0; sp < 3; sp++) {
+                        const uint32_t(&r0)[4] = aE[(oh + 2 * sp) % 5];
+                        const uint32_t(&r1)[4] = aE[(oh + 2 * sp + (sp < 2 ? 1 : 0)) % 5];  // row 5 does not exist: zero weights
+                        const uint32_t a2[4] = {r0[0], r0[1], r1[0], r1[1]};
+                        Ops<T>::mma(cE, a2, bE[sp]);
+                        Ops<T>::mma(cO, a2, bO[sp]);
+                    }
+                } else {
                 // kernel row 0 first: it reads the window slot that row h+1 is about to overwrite
                 Ops<T>::mma(cE, aE[(oh + 0) % 5], bE[0]); Ops<T>::mma(cO, aO[(oh + 0) % 5], bO[0]);
                 Ops<T>::mma(SIB_SPLIT_ACC ? dE : cE, aE[(oh + 3) % 5], bE[3]); Ops<T>::mma(SIB_SPLIT_ACC ? dO : cO, aO[(oh + 3) % 5], bO[3]);
                 Ops<T>::mma(cE, aE[(oh + 1) % 5], bE[1]); Ops<T>::mma(cO, aO[(oh + 1) % 5], bO[1]);
                 Ops<T>::mma(SIB_SPLIT_ACC ? dE : cE, aE[(oh + 4) % 5], bE[4]); Ops<T>::mma(SIB_SPLIT_ACC ? dO : cO, aO[(oh + 4) % 5], bO[4]);
                 Ops<T>::mma(cE, aE[(oh + 2) % 5], bE[2]); Ops<T>::mma(cO, aO[(oh + 2) % 5], bO[2]);
+                }
             }
             if (h + 1 < N::H) load_frags(h + 1);
             if (h >= 4) {
@@ -817,6 +843,11 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
     for (int v = 0; v < 2; v++)
         for (int kh = 0; kh < 5; kh++)
             pack_b<T>(&w[N::W_C1 + (v * 5 + kh) * 64], [&](int k, int n) -> float {
+                if (N::PACK2) {  // entry `kh` < 3 is the pair of kernel rows (2kh, 2kh+1): k 0..7 | k 8..15
+                    const int row = 2 * kh + (k >> 3), j = (k & 7) - v;
+                    if (kh > 2 || row > 4 || j < 0 || j >= 5 || n >= N::C1) return 0.f;
+                    return f1[(row * 5 + j) * N::C1 + n];
+                }
                 const int j = k - v;  // odd-column tiles read one element earlier, so their K is shifted by one
                 if (j < 0 || j >= N::K1ROW || n >= N::C1) return 0.f;
                 return f1[((kh * 5 + j / N::C) * N::C + j % N::C) * N::C1 + n];
