@@ -56,12 +56,23 @@ struct DevBufs {  // one forward's worth of device memory
     GuardScratch guard;
 };
 
+// An atomic that a std::vector element may hold: copies copy the value (slots are only copied while the engine is built).
+template <typename T>
+struct Atom {
+    std::atomic<T> v;
+    Atom(T x = T()) : v(x) {}
+    Atom(const Atom& o) : v(o.v.load()) {}
+    Atom& operator=(const Atom& o) { v.store(o.v.load()); return *this; }
+    Atom& operator=(T x) { v.store(x); return *this; }
+    operator T() const { return v.load(); }
+};
+
 struct Slot {
     // FILLING: accepting tuples. SEALED: closed to new tuples and queued for launch, but some submitter is still
     // copying its images in (writers > 0). INFLIGHT: copies and kernels issued. READY: results in h_probs.
     // HANDED: results given out by sib_poll, slot recycled at the next poll.
     enum State { FREE, FILLING, SEALED, INFLIGHT, READY, HANDED };
-    State state = FREE;
+    Atom<int> state{FREE};       // written under the engine lock; the last writer of a tuple reads it without (see written())
     float* h_in = nullptr;       // pinned, max_batch x img
     float* h_probs = nullptr;    // pinned, max_batch x ncls
     int32_t* h_argmax = nullptr; // pinned
@@ -85,7 +96,7 @@ struct Slot {
     std::vector<SideResult> side;
     std::vector<std::pair<int, int>> staged;  // (offset, n) image ranges that sit in h_in and need the H2D at launch
     size_t direct_bytes = 0;                  // bytes already sent device-ward straight from caller-pinned memory
-    int writers = 0;       // submitters that reserved room and are copying outside the lock
+    Atom<int> writers{0};  // submitters that reserved room and are copying outside the lock; they leave without it
     int flush_reason = 0;  // why it was sealed: 0 size, 1 deadline, 2 explicit
     Clock::time_point first_ts;
 };
@@ -107,7 +118,7 @@ struct sib_engine {
     std::mutex mu;
     std::condition_variable cv;
     std::thread deadline_thread;
-    bool closing = false;
+    Atom<bool> closing{false};
     sib_stats stats{};
     // synchronous path
     std::mutex sync_mu;
@@ -413,7 +424,7 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
         r = tc_prepare(m, c.precision, &e->tc);
         if (r) return fail(r);
     }
-    e->slots.resize(c.n_slots);
+    e->slots.assign((size_t)c.n_slots, Slot());
     for (auto& s : e->slots)
         if ((r = e->alloc_slot(s)) != SIB_OK) return fail(r);
     if ((r = e->alloc_slot(e->sync_slot)) != SIB_OK) return fail(r);
@@ -505,22 +516,24 @@ static int reserve(sib_engine* e, int si, uint64_t tag, int n, bool staged = tru
     }
     s.entries.push_back(Entry{tag, n, off});
     s.images += n;
-    s.writers++;
+    s.writers.v.fetch_add(1);
     e->stats.tuples++;
     e->stats.images += (uint64_t)n;
     if (s.images >= e->cfg.max_batch) e->seal_locked(si, 0);  // full: sealed now, launched when the copies are in
     return off;
 }
 
+// A submitter is done copying. No lock on the common path: the count drops, and only the writer that takes it to
+// zero looks further. Sealing (under the lock) stores SEALED and then reads the count; this side decrements and then
+// reads the state; both sequentially consistent, so at least one of the two sees the other and launches, and the
+// state check under the lock makes sure only one does.
 static void written(sib_engine* e, int si) {
-    std::unique_lock<std::mutex> lk(e->mu);
     Slot& s = e->slots[si];
-    if (--s.writers == 0) {
-        if (s.state == Slot::SEALED) e->launch_locked(si);  // notifies the pollers itself
-        else if (e->closing) e->cv.notify_all();            // sib_engine_close waits for the writers to drain
-        // otherwise nobody waits for this: waking the deadline thread once per tuple cost a futex call and a lock
-        // hand-over per tuple (the single-image tuple rate is what a Storm executor actually produces)
-    }
+    if (s.writers.v.fetch_sub(1) != 1) return;
+    if (s.state.v.load() != Slot::SEALED && !e->closing.v.load()) return;
+    std::unique_lock<std::mutex> lk(e->mu);
+    if (s.state == Slot::SEALED && s.writers == 0) e->launch_locked(si);  // notifies the pollers itself
+    else if (e->closing) e->cv.notify_all();                             // sib_engine_close waits for the writers to drain
 }
 
 extern "C" int sib_submit_f32(sib_engine* e, uint64_t tag, const float* nhwc, int n) {
@@ -556,7 +569,7 @@ extern "C" int sib_submit_pinned(sib_engine* e, uint64_t tag, const float* pinne
     if (ce != cudaSuccess) { set_error(std::string("sib_submit_pinned H2D: ") + cudaGetErrorString(ce)); return SIB_ECUDA; }
     s.direct_bytes += bytes;
     reserve(e, si, tag, n, false);  // counts this call as a writer, so a slot that just became full is only sealed
-    if (--s.writers == 0 && s.state == Slot::SEALED) e->launch_locked(si);
+    if (s.writers.v.fetch_sub(1) == 1 && s.state == Slot::SEALED) e->launch_locked(si);
     return n;
 }
 
