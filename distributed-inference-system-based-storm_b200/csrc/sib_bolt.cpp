@@ -30,6 +30,7 @@ void InferenceBolt::prepare(const Conf& conf, const TopologyContext& ctx, Output
     cfg.n_slots = conf_int(conf, "sib.slots", 0);
     cfg.guard = conf_int(conf, "sib.guard", 1);
     cfg.json_on_gpu = conf_int(conf, "sib.json.gpu", 0);
+    cfg.strict_batching = conf_int(conf, "sib.strict.batching", 0);
     auto tau = conf.find("sib.guard.tau");
     cfg.guard_tau = tau == conf.end() ? 0.0f : (float)std::atof(tau->second.c_str());
     auto pr = conf.find("sib.precision");

@@ -384,6 +384,7 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     if (c.deadline_us <= 0) c.deadline_us = 200;
     if (c.n_slots < 2) c.n_slots = 4;
     c.json_on_gpu = c.json_on_gpu ? 1 : 0;
+    c.strict_batching = c.strict_batching ? 1 : 0;
     if (c.precision != SIB_PREC_FP16 && c.precision != SIB_PREC_BF16 && c.precision != SIB_PREC_FP32) {
         set_error("precision must be SIB_PREC_FP16, SIB_PREC_BF16 or SIB_PREC_FP32");
         delete e;
@@ -520,6 +521,7 @@ static int reserve(sib_engine* e, int si, uint64_t tag, int n, bool staged = tru
     e->stats.tuples++;
     e->stats.images += (uint64_t)n;
     if (s.images >= e->cfg.max_batch) e->seal_locked(si, 0);  // full: sealed now, launched when the copies are in
+    else if (!e->cfg.strict_batching && e->fifo.empty()) e->seal_locked(si, 3);  // idle GPU: do not sit out the deadline
     return off;
 }
 
@@ -710,6 +712,9 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                 break;
             }
         }
+        // the GPU just ran dry: whatever queued up behind the batch that was handed out leaves now, not at its deadline
+        if (!e->cfg.strict_batching && e->fifo.empty() && e->filling >= 0 && e->slots[e->filling].images > 0)
+            e->seal_locked(e->filling, 3);
         if (got > 0 || timeout_us == 0) break;
         const bool pending = !e->fifo.empty() || (e->filling >= 0 && e->slots[e->filling].images > 0);
         if (!pending) break;

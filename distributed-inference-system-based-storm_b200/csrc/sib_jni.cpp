@@ -16,9 +16,10 @@ JNIEXPORT jlong JNICALL Java_dke_model_NativeInfer_open(JNIEnv* env, jclass, jby
     jsize n = env->GetArrayLength(blob);
     std::vector<jbyte> b((size_t)n);
     env->GetByteArrayRegion(blob, 0, n, b.data());
-    jint c[7] = {-1, 0, 0, 0, 0, 0, 1};
-    env->GetIntArrayRegion(cfg, 0, 7, c);
-    sib_config sc{c[0], c[1], c[2], c[3], c[4], c[5], c[6], tau, 0};
+    jint c[9] = {-1, 0, 0, 0, 0, 0, 1, 0, 0};  // device, task, max_batch, deadline_us, precision, slots, guard, json_on_gpu, strict_batching
+    const jsize nc = env->GetArrayLength(cfg);
+    env->GetIntArrayRegion(cfg, 0, nc < 9 ? nc : 9, c);
+    sib_config sc{c[0], c[1], c[2], c[3], c[4], c[5], c[6], tau, c[7], c[8]};
     sib_engine* e = nullptr;
     if (sib_engine_open(b.data(), (size_t)n, &sc, &e) != SIB_OK) return 0;
     return (jlong)(intptr_t)e;

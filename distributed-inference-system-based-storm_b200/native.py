@@ -24,7 +24,7 @@ lib = C.CDLL(LIB_PATH)
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("task_index", C.c_int32), ("max_batch", C.c_int32),
                 ("deadline_us", C.c_int32), ("precision", C.c_int32), ("n_slots", C.c_int32),
-                ("guard", C.c_int32), ("guard_tau", C.c_float), ("json_on_gpu", C.c_int32)]
+                ("guard", C.c_int32), ("guard_tau", C.c_float), ("json_on_gpu", C.c_int32), ("strict_batching", C.c_int32)]
 
 
 class Result(C.Structure):
@@ -150,11 +150,11 @@ class Engine:
 
     def __init__(self, blob: bytes, device: int = -1, task_index: int = 0, max_batch: int = 4096,
                  deadline_us: int = 200, precision: int = PREC_FP16, n_slots: int = 4, guard: bool = True,
-                 guard_tau: float = 0.0, json_on_gpu: bool = False):
+                 guard_tau: float = 0.0, json_on_gpu: bool = False, strict_batching: bool = False):
         self._h = C.c_void_p()
         self._blob = blob
         cfg = Config(device, task_index, max_batch, deadline_us, precision, n_slots, 1 if guard else 0, guard_tau,
-                     1 if json_on_gpu else 0)
+                     1 if json_on_gpu else 0, 1 if strict_batching else 0)
         rc = lib.sib_engine_open(blob, len(blob), C.byref(cfg), C.byref(self._h))
         if rc:
             raise SibError(rc, "sib_engine_open")

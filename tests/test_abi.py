@@ -31,7 +31,7 @@ def test_binding_table_covers_header(sib):
 
 def test_struct_sizes_match_header(sib):
     n = sib.native
-    assert ctypes.sizeof(n.Config) == 36
+    assert ctypes.sizeof(n.Config) == 40
     assert ctypes.sizeof(n.Result) == 40
     assert ctypes.sizeof(n.ModelInfo) == 40
     assert ctypes.sizeof(n.Stats) == 8 * (7 + 16 + 5)

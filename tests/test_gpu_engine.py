@@ -20,7 +20,7 @@ def test_submit_poll_order_and_values(sib, oracle, presets):
     m = presets["mnist-lenet5"]
     x = sib.modelspec.synthetic_images(m, 21, 300)
     _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=1000, n_slots=3) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=1000, n_slots=3, strict_batching=True) as e:
         got = []
         for i in range(300):
             while True:
@@ -46,7 +46,7 @@ def test_submit_poll_order_and_values(sib, oracle, presets):
 def test_flush_by_deadline(sib, presets):
     m = presets["mnist-lenet5"]
     x = sib.modelspec.synthetic_images(m, 22, 3)
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=4096, deadline_us=2000) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=4096, deadline_us=2000, strict_batching=True) as e:
         t0 = time.time()
         for i in range(3):
             assert e.submit_f32(i, x[i]) == 1
@@ -64,7 +64,7 @@ def test_multi_image_tuples_and_json_submit(sib, oracle, presets):
     ms = sib.modelspec
     x = ms.synthetic_images(m, 23, 5)
     _, pr = oracle.Model(m.to_blob()).forward(x)
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=8, deadline_us=500) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=8, deadline_us=500, strict_batching=True) as e:
         assert e.submit_json(7, ms.instances_json(x[:2])) == 2           # N=2 rows in one tuple (InstObj.java:8)
         assert e.submit_f32(8, x[2:5]) == 3
         assert e.submit_json(9, b'{"instances": [[[[1.0]]]') == sib.native.EJSON
@@ -91,7 +91,7 @@ def test_multi_image_tuples_and_json_submit(sib, oracle, presets):
 def test_back_pressure_is_eagain_not_deadlock(sib, presets):
     m = presets["mnist-lenet5"]
     x = sib.modelspec.synthetic_images(m, 24, 1)
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=2, deadline_us=10**6, n_slots=2) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=2, deadline_us=10**6, n_slots=2, strict_batching=True) as e:
         rcs = [e.submit_f32(i, x[0]) for i in range(6)]
         assert rcs[:4] == [1, 1, 1, 1] and sib.native.EAGAIN in rcs[4:]   # 2 slots x 2 images, nobody polled
         got = _drain(e, 4)
@@ -103,7 +103,7 @@ def test_back_pressure_is_eagain_not_deadlock(sib, presets):
 def test_close_with_pending_work(sib, presets):
     m = presets["mnist-lenet5"]
     x = sib.modelspec.synthetic_images(m, 25, 10)
-    e = sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6)
+    e = sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6, strict_batching=True)
     for i in range(10):
         e.submit_f32(i, x[i])
     e.close()  # must flush, wait and free without hanging
@@ -116,7 +116,7 @@ def test_submit_pinned_is_zero_copy_and_mixes_with_staged(sib, oracle, presets):
     _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
     pinned = torch.empty((96, 28, 28, 1), dtype=torch.float32, pin_memory=True)
     pinned.numpy()[:] = x
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=10**6, strict_batching=True) as e:
         # tuples alternate between caller-pinned memory (DMA straight from it) and staged copies, inside one batch
         for i in range(0, 96, 8):
             if (i // 8) % 2 == 0:
@@ -138,7 +138,7 @@ def test_loadgen_latency_is_bounded_by_deadline_plus_service(sib, presets):
     ms = sib.modelspec
     x = ms.synthetic_images(m, 27, 8)
     payloads = [ms.instances_json(x[i:i + 1]) for i in range(8)]
-    with sib.native.Engine(m.to_blob(), max_batch=256, deadline_us=300) as e:
+    with sib.native.Engine(m.to_blob(), max_batch=256, deadline_us=300, strict_batching=True) as e:
         sib.native.loadgen(e, payloads, 2000.0, 500, mode=sib.native.LG_JSON)          # warm-up
         r = sib.native.loadgen(e, payloads, 5000.0, 5000, mode=sib.native.LG_JSON, producers=2, want_latencies=True)
         assert r["completed"] == 5000 and r["rejected"] == 0 and r["images"] == 5000
@@ -185,3 +185,26 @@ def test_engines_on_several_threads_with_different_models(sib, presets):
     [t.start() for t in ts]
     [t.join() for t in ts]
     assert not errors, errors
+
+
+def test_eager_launches_when_idle_and_still_batches_under_load(sib, oracle, presets):
+    """Default policy (sib_config.strict_batching = 0): a tuple that finds nothing queued or in flight does not wait for the deadline; a burst that
+    arrives while that batch runs is still grouped; order and values are unchanged."""
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 71, 400)
+    _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), max_batch=256, deadline_us=2_000_000) as e:  # default: strict_batching = 0
+        t0 = time.time()
+        assert e.submit_f32(7, x[0:1]) == 1
+        out = _drain(e, 1, timeout_s=1.0)
+        assert len(out) == 1 and time.time() - t0 < 0.5          # the 2 s deadline was not waited for
+        assert out[0][0] == 7 and np.abs(out[0][1] - pr[0:1]).max() <= 1e-2
+        for i in range(1, 400):                                    # a burst: the first launches alone, the rest group up
+            while e.submit_f32(100 + i, x[i:i + 1]) == sib.native.EAGAIN:
+                _drain(e, 1, timeout_s=1.0)
+        e.flush()
+        got = out + _drain(e, 399)
+        st = e.stats()
+    assert [g[0] for g in got[1:]] == [100 + i for i in range(1, 400)]
+    assert np.abs(np.concatenate([g[1] for g in got[1:]]) - pr[1:]).max() <= 1e-2
+    assert st.flush_by_deadline == 0 and st.batches < 200          # grouped, not one launch per tuple

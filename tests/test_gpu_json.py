@@ -58,7 +58,7 @@ def test_gpu_decode_is_bit_exact_with_host_decode(sib, presets):
         ws, sep = [("", ""), (" ", " "), ("\n\t", "\n ")][k % 3]
         tuples.append(_payload(txt, m.h, m.w, m.c, ws, sep))
         want_x.append(np.array([np.float32(float(s)) for s in txt], np.float32).reshape(1, m.h, m.w, m.c))
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=32, deadline_us=10**6, json_on_gpu=True) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=32, deadline_us=10**6, json_on_gpu=True, strict_batching=True) as e:
         got = _run(e, tuples)
         st = e.stats()
     with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64) as h:
@@ -88,7 +88,7 @@ def test_gpu_decode_hands_the_unusual_to_the_host_decoder(sib, oracle, presets):
     unk = good[1].replace(b'"instances"', b'"inputs"')
     small = b'{"instances":[[[[1.0,2.0]]]]}'                                  # not 28x28x1; shorter than a real tuple
     tuples = [good[0], two, dup, nul, trail, trunc, unk, small, good[3]]
-    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=16, deadline_us=10**6, json_on_gpu=True) as e:
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=16, deadline_us=10**6, json_on_gpu=True, strict_batching=True) as e:
         got = _run(e, tuples)
     EJ, ES = sib.native.EJSON, sib.native.ESHAPE
     assert got[0][3] == 0 and np.abs(got[0][1] - pr[0:1]).max() <= 1e-5

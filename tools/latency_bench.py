@@ -21,14 +21,14 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
 import numpy as np  # noqa: E402
 
 
-def gpu_point(sib, blob, payloads, mode, rate, seconds, producers, max_batch, deadline_us, poisson=False, json_on_gpu=False):
+def gpu_point(sib, blob, payloads, mode, rate, seconds, producers, max_batch, deadline_us, poisson=False, json_on_gpu=False, strict=False):
     n = max(1000, int(rate * seconds))
-    with sib.native.Engine(blob, max_batch=max_batch, deadline_us=deadline_us, n_slots=6, json_on_gpu=json_on_gpu) as e:
+    with sib.native.Engine(blob, max_batch=max_batch, deadline_us=deadline_us, n_slots=6, json_on_gpu=json_on_gpu, strict_batching=strict) as e:
         sib.native.loadgen(e, payloads, min(rate, 20000.0), 2000, mode=mode, producers=producers)  # warm-up
         r = sib.native.loadgen(e, payloads, rate, n, mode=mode, producers=producers, poisson=poisson)
         st = e.stats()
     return {"arm": "b200", "level": ("T2 json->json" + (" (gpu decode)" if json_on_gpu else " (host decode)")) if mode == sib.native.LG_JSON else "T1 f32->probs",
-            "rate_tuples_s": rate, "tuples": n, "producers": producers, "max_batch": max_batch, "deadline_us": deadline_us,
+            "rate_tuples_s": rate, "tuples": n, "producers": producers, "max_batch": max_batch, "deadline_us": deadline_us, "strict_batching": bool(strict),
             "achieved_tuples_s": r["achieved_tuples_per_s"], "p50_us": r["p50_ns"] / 1e3, "p99_us": r["p99_ns"] / 1e3,
             "p999_us": r["p999_ns"] / 1e3, "max_us": r["max_ns"] / 1e3, "late_submits": r["late_submits"],
             "eagain": r["eagain_spins"], "batches": int(st.batches), "by_deadline": int(st.flush_by_deadline),
@@ -70,6 +70,11 @@ def main():
             print(json.dumps(gpu_point(sib, blob, jp, sib.native.LG_JSON, rate, args.seconds, prod, mb, dl, args.poisson, json_on_gpu=True)), flush=True)
         for rate in (10_000, 100_000, 1_000_000):
             print(json.dumps(gpu_point(sib, blob, fp, sib.native.LG_F32, rate, args.seconds, prod, mb, dl, args.poisson)), flush=True)
+    # sib_config.strict_batching = 1: batches leave by size and deadline only (the default also launches when the GPU is idle)
+    for rate in (1_000, 10_000, 100_000, 400_000):
+        print(json.dumps(gpu_point(sib, blob, jp, sib.native.LG_JSON, rate, args.seconds, prod, 512, 200, args.poisson, json_on_gpu=True, strict=True)), flush=True)
+    for rate in (1_000, 10_000, 100_000, 1_000_000):
+        print(json.dumps(gpu_point(sib, blob, fp, sib.native.LG_F32, rate, args.seconds, prod, 512, 200, args.poisson, strict=True)), flush=True)
     for rate in (1_000, 10_000):
         print(json.dumps(cpu_point(oracle, om, jp, True, rate, args.seconds, cores)), flush=True)
     for rate in (10_000, 100_000):
