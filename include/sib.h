@@ -77,7 +77,8 @@ typedef struct sib_result {
 
 typedef struct sib_stats {
     uint64_t tuples, images, batches;
-    uint64_t flush_by_size, flush_by_deadline, flush_explicit;
+    uint64_t flush_by_size, flush_by_deadline,
+        flush_explicit; /* sib_flush, engine close, and launches made because the GPU was idle (strict_batching = 0) */
     uint64_t guard_recomputed; /* images the margin guard re-ran in fp32 */
     uint64_t batch_hist[16];   /* batch sizes, bucket b counts batches with 2^b <= images < 2^(b+1) */
     uint64_t h2d_bytes, d2h_bytes;
