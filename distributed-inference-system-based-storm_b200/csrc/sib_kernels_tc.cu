@@ -65,6 +65,9 @@ constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #ifndef SIB_CONV1_PACK2
 #define SIB_CONV1_PACK2 1
 #endif
+#ifndef SIB_SKIP_EMPTY
+#define SIB_SKIP_EMPTY 1      // conv1 spans / conv2 tiles that hold no real image are not computed (small launches)
+#endif
 #ifndef SIB_REG_STAGE
 #define SIB_REG_STAGE 1       // 0 forces the cp.async staging ring (kept for heights that are not a multiple of 2 batches)
 #endif
@@ -331,6 +334,15 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         const int n_gs = SIB_DYN_SPANS ? claim() : gs + kConv1Warps;
         span_src(n_gs, n_img0, n_valid);
         const float* n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS) : src;
+        // A span whose first column already lies past the last image has nothing to compute (the tail of a batch:
+        // with 1 image in a launch, 13 of the pair's 14 spans). It only keeps the slot protocol going. Image indices
+        // grow with gs, so every later span of this warp is empty as well and the prefetch state no longer matters.
+        if (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= P.n) {
+            mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
+            mbar_arrive(&p1_full[buf]);
+            gs = n_gs; valid = n_valid; src = n_src; img0 = n_img0;
+            continue;
+        }
 
         // fragment offsets into a staged row (halves)
         const int p0 = 32 * s;
@@ -515,6 +527,12 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
 
         mbar_wait(&p1_full[buf1], use1 & 1);
         mbar_wait(&p2_empty[buf2], (use2 & 1) ^ 1);
+        // a tile whose first column lies past the last image: nothing to compute, keep the slot protocol going
+        if (SIB_SKIP_EMPTY && !SIB_FC_IN_CONV2 && (int)(blockIdx.x + Qi * gridDim.x) * kPair + (lq & 1) * kG + (16 * tile) / N::OW2 >= P.n) {  // warp-uniform
+            mbar_arrive(&p1_empty[buf1]);
+            mbar_arrive(&p2_full[buf2]);
+            continue;
+        }
 
         uint32_t a[5][2][4];
         float prev[4] = {0.f, 0.f, 0.f, 0.f};
