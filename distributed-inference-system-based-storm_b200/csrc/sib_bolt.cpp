@@ -35,7 +35,11 @@ void InferenceBolt::prepare(const Conf& conf, const TopologyContext& ctx, Output
     cfg.guard_tau = tau == conf.end() ? 0.0f : (float)std::atof(tau->second.c_str());
     auto pr = conf.find("sib.precision");
     cfg.precision = pr == conf.end() ? SIB_PREC_FP16 : pr->second == "fp32" ? SIB_PREC_FP32 : pr->second == "bf16" ? SIB_PREC_BF16 : SIB_PREC_FP16;
-    int rc = sib_engine_open(blob_.data(), blob_.size(), &cfg, &engine_);
+    // sib.shared = 1: the bolts of this worker process that load the same model with the same settings share one engine
+    // (one batcher, one set of streams, one weight upload); each still sees only its own tuples, in its own order
+    shared_ = conf_int(conf, "sib.shared", 0) != 0;
+    int rc = shared_ ? sib_client_open(blob_.data(), blob_.size(), &cfg, &client_)
+                     : sib_engine_open(blob_.data(), blob_.size(), &cfg, &engine_);
     // the reference lets SavedModelBundle.load throw out of prepare(); so do we
     if (rc != SIB_OK) throw std::runtime_error(std::string("InferenceBolt.prepare: ") + sib_last_error());
     stop_ = false;
@@ -69,7 +73,7 @@ void InferenceBolt::completion_main() {
             continue;
         }
         lk.unlock();
-        int n = sib_poll(engine_, res.data(), (int)res.size(), 2000);
+        int n = shared_ ? sib_client_poll(client_, res.data(), (int)res.size(), 2000) : sib_poll(engine_, res.data(), (int)res.size(), 2000);
         lk.lock();
         for (int i = 0; i < n; i++) {
             emit_front_nulls_locked();
@@ -103,7 +107,8 @@ void InferenceBolt::execute(const Tuple& tuple) {
         cv_.notify_all();
     }
     for (;;) {
-        int rc = sib_submit_json(engine_, seq_, inputJson.data(), inputJson.size());
+        int rc = shared_ ? sib_client_submit_json(client_, seq_, inputJson.data(), inputJson.size())
+                         : sib_submit_json(engine_, seq_, inputJson.data(), inputJson.size());
         if (rc > 0) {
             seq_++;
             return;
@@ -129,8 +134,8 @@ void InferenceBolt::execute(const Tuple& tuple) {
 }
 
 void InferenceBolt::cleanup() {
-    if (!engine_) return;
-    sib_flush(engine_);
+    if (!engine_ && !client_) return;
+    if (shared_) sib_client_flush(client_); else sib_flush(engine_);
     {
         std::unique_lock<std::mutex> lk(mu_);
         cv_.notify_all();
@@ -139,8 +144,9 @@ void InferenceBolt::cleanup() {
         cv_.notify_all();
     }
     if (completion_.joinable()) completion_.join();
-    sib_engine_close(engine_);
+    if (shared_) sib_client_close(client_); else sib_engine_close(engine_);
     engine_ = nullptr;
+    client_ = nullptr;
 }
 
 }  // namespace model

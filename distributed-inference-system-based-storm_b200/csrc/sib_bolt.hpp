@@ -80,6 +80,8 @@ private:
 
     std::string blob_;
     sib_engine* engine_ = nullptr;
+    sib_client* client_ = nullptr;  // sib.shared = 1: a view of the worker process's shared engine instead
+    bool shared_ = false;
     OutputCollector* collector_ = nullptr;
     std::mutex mu_;
     std::condition_variable cv_;

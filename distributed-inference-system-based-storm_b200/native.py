@@ -54,6 +54,13 @@ SYMBOLS = {
     "sib_engine_open": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "sib_engine_close": (C.c_int, [C.c_void_p]),
     "sib_engine_info": (C.c_int, [C.c_void_p, C.POINTER(ModelInfo), C.POINTER(Config)]),
+    "sib_client_open": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(Config), C.POINTER(C.c_void_p)]),
+    "sib_client_close": (C.c_int, [C.c_void_p]),
+    "sib_client_submit_json": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_size_t]),
+    "sib_client_submit_f32": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
+    "sib_client_poll": (C.c_int, [C.c_void_p, C.POINTER(Result), C.c_int, C.c_int]),
+    "sib_client_flush": (C.c_int, [C.c_void_p]),
+    "sib_client_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "sib_submit_json": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_size_t]),
     "sib_submit_f32": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
     "sib_submit_pinned": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
@@ -143,6 +150,63 @@ def float_to_string(x) -> str:
     buf = C.create_string_buffer(32)
     n = lib.sib_float_to_string(C.c_float(float(np.float32(x))), buf)
     return buf.raw[:n].decode()
+
+
+class Client:
+    """A bolt's view of the process-wide engine shared by co-located bolts (include/sib.h, sib_client_*)."""
+
+    def __init__(self, blob: bytes, img_elems: int, **cfg_kw):
+        d = dict(device=-1, task_index=0, max_batch=4096, deadline_us=200, precision=PREC_FP16, n_slots=4, guard=1,
+                 guard_tau=0.0, json_on_gpu=0, strict_batching=0)
+        d.update(cfg_kw)
+        cfg = Config(*[d[k] for k, _ in Config._fields_])
+        self._h = C.c_void_p()
+        rc = lib.sib_client_open(blob, len(blob), C.byref(cfg), C.byref(self._h))
+        if rc:
+            raise SibError(rc, "sib_client_open")
+        self.img_elems = img_elems
+        self._res = (Result * 1024)()
+
+    def close(self):
+        if self._h:
+            lib.sib_client_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def submit_f32(self, tag: int, x: np.ndarray) -> int:
+        x = np.ascontiguousarray(x, np.float32)
+        return int(lib.sib_client_submit_f32(self._h, tag, _p(x), x.size // self.img_elems))
+
+    def submit_json(self, tag: int, text: bytes) -> int:
+        return int(lib.sib_client_submit_json(self._h, tag, text, len(text)))
+
+    def flush(self):
+        lib.sib_client_flush(self._h)
+
+    def stats(self) -> Stats:
+        st = Stats()
+        lib.sib_client_stats(self._h, C.byref(st))
+        return st
+
+    def poll(self, max_results: int = 1024, timeout_us: int = 0):
+        """-> list of (tag, probs[n,ncls] copy, argmax[n] copy, status)."""
+        n = lib.sib_client_poll(self._h, self._res, min(max_results, 1024), timeout_us)
+        if n < 0:
+            raise SibError(n, "sib_client_poll")
+        out = []
+        for i in range(n):
+            r = self._res[i]
+            if r.n == 0 or not r.probs:
+                out.append((int(r.tag), None, None, int(r.status)))
+                continue
+            out.append((int(r.tag), np.ctypeslib.as_array(r.probs, (r.n, r.n_classes)).copy(),
+                        np.ctypeslib.as_array(r.argmax, (r.n,)).copy(), int(r.status)))
+        return out
 
 
 class Engine:

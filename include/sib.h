@@ -107,6 +107,23 @@ int sib_engine_open(const void *model_blob, size_t n, const sib_config *cfg, sib
 int sib_engine_close(sib_engine *e); /* flushes, waits for in-flight batches, frees everything */
 int sib_engine_info(sib_engine *e, sib_model_info *out, sib_config *effective_cfg);
 
+/* ---- one engine for all the bolts of a worker process ------------------------------------------------------------
+ * Storm puts several executors of the bolt into one worker JVM (MainTopology.java:27, :65-66); the reference gives
+ * each its own model copy (InferenceBolt.java:57-58). sib_client_open returns a view of a process-wide,
+ * reference-counted engine keyed by (resolved device, model bytes, configuration): co-located bolts then fill the
+ * same batches through one set of streams and one weight upload. A client sees only its own tuples, in its own
+ * submission order; its results live in client-owned memory until its next sib_client_poll, so one bolt's polling
+ * pace never holds the others back. Same return codes as the sib_engine calls of the same name. The last
+ * sib_client_close closes the engine. No counterpart in the reference. */
+typedef struct sib_client sib_client;
+int sib_client_open(const void *model, size_t n, const sib_config *cfg, sib_client **out);
+int sib_client_close(sib_client *c);
+int sib_client_submit_json(sib_client *c, uint64_t tag, const char *utf8, size_t len);
+int sib_client_submit_f32(sib_client *c, uint64_t tag, const float *nhwc, int n);
+int sib_client_poll(sib_client *c, sib_result *out, int max, int timeout_us);
+int sib_client_flush(sib_client *c);
+int sib_client_stats(sib_client *c, sib_stats *out); /* of the shared engine */
+
 /* ---- per-tuple path: replaces the body of InferenceBolt.execute() (InferenceBolt.java:69-100) --------- */
 
 /* readValue(inputJson, InstObj.class) + Tensor.create(data) (InferenceBolt.java:76-80): decodes

@@ -98,3 +98,33 @@ def test_multi_row_tuple_is_a_documented_superset(sib, presets):
     msg = [e[1] for e in col.events if e[0] == "emit"][0]
     assert np.array(json.loads(msg)["predictions"]).shape == (3, 10)
     bolt.close()
+
+
+def test_two_bolts_sharing_one_engine_keep_the_contract(sib, oracle, presets):
+    """sib.shared = 1: two executors of one worker process, one engine underneath. Each bolt still emits and acks
+    exactly its own tuples, once, in its own arrival order, nulls included (InferenceBolt.java:92-99)."""
+    m = presets["mnist-lenet5"]
+    ms = sib.modelspec
+    om = oracle.Model(m.to_blob())
+    bolts = [_bolt(sib, m.to_blob(), sib_shared=1) for _ in range(2)]
+    x = ms.synthetic_images(m, 33, 80)
+    payloads = [ms.instances_json(x[i:i + 1]) for i in range(80)]
+    payloads[7] = b'{"instances": [[[[0.5'
+    for i, p in enumerate(payloads):                            # tuples alternate between the two executors
+        B, bolt, col = bolts[i % 2]
+        bolt.execute(B.Tuple(i, p))
+    for B, bolt, col in bolts:
+        bolt.cleanup()
+    for k, (B, bolt, col) in enumerate(bolts):
+        mine = list(range(k, 80, 2))
+        assert [e[1] for e in col.events if e[0] == "ack"] == mine
+        emits = [e[1] for e in col.events if e[0] == "emit"]
+        assert len(emits) == len(mine)
+        for i, msg in zip(mine, emits):
+            if i == 7:
+                assert msg is None
+                continue
+            got = np.array(json.loads(msg)["predictions"], np.float32)
+            ref = np.array(json.loads(om.execute(payloads[i]))["predictions"], np.float32)
+            assert np.abs(got - ref).max() <= 1e-5
+        bolt.close()

@@ -208,3 +208,49 @@ def test_eager_launches_when_idle_and_still_batches_under_load(sib, oracle, pres
     assert [g[0] for g in got[1:]] == [100 + i for i in range(1, 400)]
     assert np.abs(np.concatenate([g[1] for g in got[1:]]) - pr[1:]).max() <= 1e-2
     assert st.flush_by_deadline == 0 and st.batches < 200          # grouped, not one launch per tuple
+
+
+def test_co_located_bolts_share_one_engine(sib, oracle, presets):
+    """sib_client_*: three bolts of one worker process open the same model: one engine, common batches, and every
+    bolt gets back exactly its own tuples, in its own order, with the right values (threading row)."""
+    import threading
+
+    m = presets["mnist-lenet5"]
+    x = sib.modelspec.synthetic_images(m, 72, 600)
+    _, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    img = m.h * m.w * m.c
+    kw = dict(precision=sib.native.PREC_FP32, max_batch=128, deadline_us=300)
+    clients = [sib.native.Client(m.to_blob(), img, task_index=t * sib.native.device_count(), **kw) for t in range(3)]
+    other = sib.native.Client(m.to_blob(), img, precision=sib.native.PREC_FP32, max_batch=64, deadline_us=300)  # another cfg: its own engine
+    got = [[] for _ in clients]
+    errors = []
+
+    def run(ci):
+        try:
+            c = clients[ci]
+            mine = list(range(ci, 600, 3))
+            sent = 0
+            while len(got[ci]) < len(mine):
+                while sent < len(mine):
+                    rc = c.submit_f32(1000 * ci + sent, x[mine[sent]:mine[sent] + 1])
+                    if rc == sib.native.EAGAIN:
+                        break
+                    assert rc == 1, rc
+                    sent += 1
+                got[ci] += c.poll(timeout_us=2000)
+        except Exception as ex:  # noqa: BLE001
+            errors.append(repr(ex))
+
+    ts = [threading.Thread(target=run, args=(i,)) for i in range(3)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors
+    st = clients[0].stats()
+    assert st.tuples == 600 and st.batches < 600          # one engine saw all three bolts' tuples and batched them
+    assert other.stats().tuples == 0
+    for ci in range(3):
+        mine = list(range(ci, 600, 3))
+        assert [g[0] for g in got[ci]] == [1000 * ci + k for k in range(len(mine))]
+        assert np.abs(np.concatenate([g[1] for g in got[ci]]) - pr[mine]).max() <= 1e-5
+    for c in clients + [other]:
+        c.close()
