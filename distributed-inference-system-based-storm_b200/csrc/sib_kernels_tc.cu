@@ -65,6 +65,9 @@ constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #ifndef SIB_CONV1_PACK2
 #define SIB_CONV1_PACK2 1
 #endif
+#ifndef SIB_TMA_WEIGHTS
+#define SIB_TMA_WEIGHTS 1     // dense-layer fragments enter shared memory by cp.async.bulk (0: copied by all threads before the start)
+#endif
 #ifndef SIB_SKIP_EMPTY
 #define SIB_SKIP_EMPTY 1      // conv1 spans / conv2 tiles that hold no real image are not computed (small launches)
 #endif
@@ -153,7 +156,8 @@ struct Net {
     static constexpr int S_BAR = ((S_STAGE + ((REG_STAGE || SIB_CONV1_UMMA) ? 0 : kConv1Warps * PD * STAGE_ROW) + 7) / 8) * 8;
     static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2;
     static constexpr int B_UA = 2 * NB1 + 4, B_UDF = B_UA + 16, B_UDE = B_UDF + 8;  // tcgen05 conv1: a_full[8] a_free[8], d_full[4] (+4 unused), d_empty[4] (+4 unused)
-    static constexpr int N_BAR = SIB_CONV1_UMMA ? B_UDE + 8 : 2 * NB1 + 4;
+    static constexpr int B_FCW = SIB_CONV1_UMMA ? B_UDE + 8 : 2 * NB1 + 4;  // fc weight image has landed (bulk copy)
+    static constexpr int N_BAR = B_FCW + 1;
     static constexpr int S_TMEM = S_BAR + N_BAR * 8;                       // TMEM base address handed out by tcgen05.alloc
     static constexpr int S_TOTAL = S_TMEM + 8;
     static_assert(S_P1 % 16 == 0 && S_P2 % 16 == 0 && S_H1 % 16 == 0 && S_RING % 16 == 0 && S_STAGE % 16 == 0 && S_BAR % 8 == 0, "align");
@@ -624,6 +628,7 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
         const uint16_t* p2 = reinterpret_cast<const uint16_t*>(smem + N::S_P2) + buf * N::P2_BUF;
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
         mbar_wait(&p2_full[buf], use & 1);
+        mbar_wait(bars + N::B_FCW, 0);  // the weight image is in (completes once; later waits fall through)
         // ---- fc1: [16 x FEAT] . [FEAT x 120]: 15 N tiles = 15 independent accumulator chains
         // (h1 columns 120..127 stay zero from the set-up; fc2's K padding multiplies them by zero weights)
         {
@@ -774,9 +779,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // ---- one-time set-up: fc weight fragments + biases into shared memory, zero the rings, init barriers
     {
+#if !SIB_TMA_WEIGHTS
         const uint4* src = reinterpret_cast<const uint4*>(P.wpack + N::W_F1);
         uint4* dst = reinterpret_cast<uint4*>(smem + N::S_FCW);
         for (int i = threadIdx.x; i < N::S_FCW_BYTES / 16; i += blockDim.x) dst[i] = src[i];
+#endif
         float* b = reinterpret_cast<float*>(smem + N::S_BIAS);
         for (int i = threadIdx.x; i < 264; i += blockDim.x) b[i] = reinterpret_cast<const float*>(P.wpack + N::W_BIAS)[i];
         uint32_t* z = reinterpret_cast<uint32_t*>(smem + N::S_P1);
@@ -792,7 +799,9 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
 #endif
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
+#if !SIB_CONV1_UMMA
             *reinterpret_cast<uint32_t*>(smem + N::S_TMEM) = 0u;  // mma.sync build: the conv1 span counter lives here
+#endif
 #if SIB_CONV1_UMMA
             for (int i = 0; i < 8; i++) mbar_init(&bars[N::B_UA + i], 128);     // a_full : every thread of the team that owns the pair
             for (int i = 8; i < 16; i++) mbar_init(&bars[N::B_UA + i], 2);      // a_free : one tcgen05.commit per issuer
@@ -807,6 +816,21 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
                 mbar_init(&bars[N::B_P2F + i], 2 * N::TILES2 * 32);   // p2_full : two slots of conv2 tiles
                 mbar_init(&bars[N::B_P2E + i], 32);                   // p2_empty: every lane of the warp that runs the pair's dense head
             }
+            mbar_init(&bars[N::B_FCW], 1);
+#if SIB_TMA_WEIGHTS
+            // The 121 KB of dense-layer fragments come in by bulk async copies (TMA unit, no register stop-over) that
+            // complete on an mbarrier: only the dense head waits for them, the conv warps start at once.
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bars[N::B_FCW])), "r"((uint32_t)N::S_FCW_BYTES) : "memory");
+            constexpr int kChunk = 16384;
+            for (int off = 0; off < N::S_FCW_BYTES; off += kChunk) {
+                const int bytes = N::S_FCW_BYTES - off < kChunk ? N::S_FCW_BYTES - off : kChunk;
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem + N::S_FCW + off)),
+                             "l"(reinterpret_cast<const char*>(P.wpack + N::W_F1) + off), "r"((uint32_t)bytes), "r"(smem_u32(&bars[N::B_FCW])) : "memory");
+            }
+#else
+            mbar_arrive(&bars[N::B_FCW]);
+#endif
         }
     }
 #if SIB_CONV1_UMMA
