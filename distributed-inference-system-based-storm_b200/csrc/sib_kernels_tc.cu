@@ -65,6 +65,9 @@ constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #ifndef SIB_CONV1_PACK2
 #define SIB_CONV1_PACK2 1
 #endif
+#ifndef SIB_CONV2_SPLIT
+#define SIB_CONV2_SPLIT 0
+#endif
 #ifndef SIB_TMA_WEIGHTS
 #define SIB_TMA_WEIGHTS 1     // dense-layer fragments enter shared memory by cp.async.bulk (0: copied by all threads before the start)
 #endif
@@ -564,6 +567,19 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
                 c0[i] = SIB_BIAS_IN_ACC2 ? ((i & 1) ? bias01 : bias00) : 0.f;
                 c1[i] = SIB_BIAS_IN_ACC2 ? ((i & 1) ? bias11 : bias10) : 0.f;
             }
+#if SIB_CONV2_SPLIT
+            // 8 chains: kernel rows 1 and 3 accumulate apart from rows 0, 2, 4 (dependent mma twice as far apart)
+            float e0[4] = {0.f, 0.f, 0.f, 0.f}, f0[4] = {0.f, 0.f, 0.f, 0.f}, e1[4] = {0.f, 0.f, 0.f, 0.f}, f1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int kh = 0; kh < 5; kh++) {
+                Ops<T>::mma((kh & 1) ? e0 : c0, a[(oh + kh) % 5][0], bW[kh][0][0]);
+                Ops<T>::mma((kh & 1) ? e1 : c1, a[(oh + kh) % 5][0], bW[kh][0][1]);
+                Ops<T>::mma((kh & 1) ? f0 : d0, a[(oh + kh) % 5][1], bW[kh][1][0]);
+                Ops<T>::mma((kh & 1) ? f1 : d1, a[(oh + kh) % 5][1], bW[kh][1][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) { c0[i] += e0[i]; c1[i] += e1[i]; d0[i] += f0[i]; d1[i] += f1[i]; }
+#else
 #pragma unroll
             for (int kh = 0; kh < 5; kh++) {
                 Ops<T>::mma(c0, a[(oh + kh) % 5][0], bW[kh][0][0]);
@@ -571,6 +587,7 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
                 Ops<T>::mma(d0, a[(oh + kh) % 5][1], bW[kh][1][0]);
                 Ops<T>::mma(d1, a[(oh + kh) % 5][1], bW[kh][1][1]);
             }
+#endif
             // pool over the column pair (rows g / g+8 of the tile)
             const float h[4] = {fmaxf(c0[0] + d0[0], c0[2] + d0[2]), fmaxf(c0[1] + d0[1], c0[3] + d0[3]),
                                 fmaxf(c1[0] + d1[0], c1[2] + d1[2]), fmaxf(c1[1] + d1[1], c1[3] + d1[3])};
