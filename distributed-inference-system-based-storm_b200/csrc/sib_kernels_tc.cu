@@ -7,7 +7,7 @@
 //   * one persistent CTA per SM; every fc weight lives in shared memory as pre-swizzled mma B fragments for the
 //     whole launch, conv weights live in registers of the warps that use them;
 //   * warps are specialised and pipelined through shared-memory rings with mbarriers, 8 images per ring slot:
-//       conv1 warps: stream fp32 NHWC rows from HBM (128-bit coalesced loads, 8 rows in flight per warp),
+//       conv1 warps: stream fp32 NHWC rows from HBM (128-bit coalesced loads, 4 rows in flight per warp in registers),
 //                    convert to half precision into a 2-row private staging ring, build im2col A fragments with a
 //                    5-row sliding register window (each staged row is read once and feeds 5 kernel rows),
 //                    mma.sync m16n8k16, bias+ReLU+2x2 maxpool fused in registers (even/odd column tiles make the
@@ -15,10 +15,13 @@
 //       conv2 warps: same sliding window over p1 rows, N=16, pool thread-local by tile-row permutation -> p2 ring;
 //       fc warps   : 16-image M tiles: 400(256)->120->84->10, bias+ReLU fused, then a quad-shuffle softmax /
 //                    argmax / top1-top2 margin, and the margin guard's compaction list.
-//   * why mma.sync and not tcgen05 here: the contractions are N=6 and N=16 wide with K=75/150; the im2col operand
-//     cannot be described to a tcgen05 shared-memory descriptor without materialising it (5-25x the bytes), and
-//     shared-memory operand bandwidth, not MMA issue, is then the limiter. Register-resident sliding windows avoid
-//     the expansion. Measured mma.sync m16n8k16 rate on this B200: 557 TFLOP/s (profiles/microbench_r01.jsonl).
+//   * the dense-layer fragments (121 KB) arrive by cp.async.bulk on an mbarrier; only the dense head waits for them;
+//   * why mma.sync is the default and tcgen05 the option (SIB_CONV1_UMMA): the contractions are N=6 and N=16 wide with
+//     K=75/150. A tcgen05 operand read from shared memory costs 4 KB per M128xK16 mma at the 128 B/clk shared-memory
+//     pipe (39-48 clk per mma measured, tools/tcgen05_probe2.cu) whether or not a sliding-window descriptor avoids the
+//     im2col copy; with the operand in TMEM the mma is fast (9 clk) but the im2col rows still pass through registers,
+//     and the variant built that way reaches 210 M img/s against 230 M here. Register-resident sliding
+//     windows feed mma.sync m16n8k16 at 557 TFLOP/s on this B200 (profiles/microbench_r01.jsonl).
 //
 // Operand type is a template parameter: __half (default: 11-bit significand, max logit error 2e-2 on the presets)
 // or __nv_bfloat16 (8-bit significand, ~1e-1). Accumulation is always fp32.
@@ -39,6 +42,7 @@ namespace {
 // each, 4 warps only 128. Two layouts were measured (tools/sweep_tc.sh, profiles/ncu_tc_r01_notes.md):
 //   8 conv1 + 3 conv2 + 1 fc, 168 regs, two 4-row prefetch batches, split accumulator chains: 205 M img/s
 //  12 conv1 + 3 conv2 + 1 fc, 128 regs, two 2-row prefetch batches, single chains (fits with 8 B spill): 216 M img/s
+//  (230 M after the later trims: no L2 prefetch, no dead adds in the conv1 epilogue, bulk-copied dense weights)
 // The second is the default: a 4th warp per sub-partition hides more of the mma / shared-memory latency than the
 // extra registers bought. Each sub-partition hosts 3 conv1 warps + (a conv2 warp | the fc warp).
 #ifndef SIB_CONV1_UMMA
