@@ -10,37 +10,56 @@
 
 #include "../../include/sib.h"
 
+// One Java long = one JHandle: the executor's own engine, or (cfg[9] = 1, Storm conf sib.shared) its view of the
+// worker process's shared engine (sib_client_*).
+struct JHandle {
+    sib_engine* e = nullptr;
+    sib_client* c = nullptr;
+};
+
 extern "C" {
 
 JNIEXPORT jlong JNICALL Java_dke_model_NativeInfer_open(JNIEnv* env, jclass, jbyteArray blob, jintArray cfg, jfloat tau) {
     jsize n = env->GetArrayLength(blob);
     std::vector<jbyte> b((size_t)n);
     env->GetByteArrayRegion(blob, 0, n, b.data());
-    jint c[9] = {-1, 0, 0, 0, 0, 0, 1, 0, 0};  // device, task, max_batch, deadline_us, precision, slots, guard, json_on_gpu, strict_batching
+    jint c[10] = {-1, 0, 0, 0, 0, 0, 1, 0, 0, 0};  // device, task, max_batch, deadline_us, precision, slots, guard, json_on_gpu, strict_batching, shared
     const jsize nc = env->GetArrayLength(cfg);
-    env->GetIntArrayRegion(cfg, 0, nc < 9 ? nc : 9, c);
+    env->GetIntArrayRegion(cfg, 0, nc < 10 ? nc : 10, c);
     sib_config sc{c[0], c[1], c[2], c[3], c[4], c[5], c[6], tau, c[7], c[8]};
-    sib_engine* e = nullptr;
-    if (sib_engine_open(b.data(), (size_t)n, &sc, &e) != SIB_OK) return 0;
-    return (jlong)(intptr_t)e;
+    JHandle* h = new JHandle;
+    const int rc = c[9] ? sib_client_open(b.data(), (size_t)n, &sc, &h->c) : sib_engine_open(b.data(), (size_t)n, &sc, &h->e);
+    if (rc != SIB_OK) { delete h; return 0; }
+    return (jlong)(intptr_t)h;
 }
 
-JNIEXPORT void JNICALL Java_dke_model_NativeInfer_close(JNIEnv*, jclass, jlong h) { sib_engine_close((sib_engine*)(intptr_t)h); }
+JNIEXPORT void JNICALL Java_dke_model_NativeInfer_close(JNIEnv*, jclass, jlong hh) {
+    JHandle* h = (JHandle*)(intptr_t)hh;
+    if (!h) return;
+    if (h->c) sib_client_close(h->c); else sib_engine_close(h->e);
+    delete h;
+}
 
-JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_submitJson(JNIEnv* env, jclass, jlong h, jlong tag, jbyteArray utf8) {
+JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_submitJson(JNIEnv* env, jclass, jlong hh, jlong tag, jbyteArray utf8) {
+    JHandle* h = (JHandle*)(intptr_t)hh;
     jsize n = env->GetArrayLength(utf8);
     jbyte* p = (jbyte*)env->GetPrimitiveArrayCritical(utf8, nullptr);   // no copy: decoded straight into the pinned slot
-    jint rc = sib_submit_json((sib_engine*)(intptr_t)h, (uint64_t)tag, (const char*)p, (size_t)n);
+    jint rc = h->c ? sib_client_submit_json(h->c, (uint64_t)tag, (const char*)p, (size_t)n)
+                   : sib_submit_json(h->e, (uint64_t)tag, (const char*)p, (size_t)n);
     env->ReleasePrimitiveArrayCritical(utf8, p, JNI_ABORT);
     return rc;
 }
 
-JNIEXPORT void JNICALL Java_dke_model_NativeInfer_flush(JNIEnv*, jclass, jlong h) { sib_flush((sib_engine*)(intptr_t)h); }
+JNIEXPORT void JNICALL Java_dke_model_NativeInfer_flush(JNIEnv*, jclass, jlong hh) {
+    JHandle* h = (JHandle*)(intptr_t)hh;
+    if (h->c) sib_client_flush(h->c); else sib_flush(h->e);
+}
 
-JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_pollJson(JNIEnv* env, jclass, jlong h, jlongArray tags, jobjectArray msgs, jint timeout_us) {
+JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_pollJson(JNIEnv* env, jclass, jlong hh, jlongArray tags, jobjectArray msgs, jint timeout_us) {
+    JHandle* h = (JHandle*)(intptr_t)hh;
     const int cap = env->GetArrayLength(tags);
     std::vector<sib_result> res((size_t)cap);
-    int n = sib_poll((sib_engine*)(intptr_t)h, res.data(), cap, timeout_us);
+    int n = h->c ? sib_client_poll(h->c, res.data(), cap, timeout_us) : sib_poll(h->e, res.data(), cap, timeout_us);
     std::vector<char> buf(1 << 14);
     for (int i = 0; i < n; i++) {
         jlong t = (jlong)res[i].tag;

@@ -49,7 +49,7 @@ public class InferenceBolt extends BaseRichBolt {
         int prec = p.equals("fp32") ? 2 : p.equals("bf16") ? 1 : 0;
         int[] cfg = { conf(map, "sib.device", -1), ctx.getThisTaskIndex(), conf(map, "sib.max.batch", 0),
                       conf(map, "sib.deadline.us", 0), prec, conf(map, "sib.slots", 0), conf(map, "sib.guard", 1),
-                      conf(map, "sib.json.gpu", 0), conf(map, "sib.strict.batching", 0) };
+                      conf(map, "sib.json.gpu", 0), conf(map, "sib.strict.batching", 0), conf(map, "sib.shared", 0) };
         engine = NativeInfer.open(blob, cfg, 0f);
         if (engine == 0) throw new RuntimeException("InferenceBolt.prepare: " + NativeInfer.lastError());
         completion = new Thread(this::completionLoop, "sib-completion");

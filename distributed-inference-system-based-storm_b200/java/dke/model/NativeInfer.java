@@ -1,7 +1,8 @@
 package dke.model;
 
 /**
- * JNI face of libsib.so (include/sib.h). One long handle = one sib_engine.
+ * JNI face of libsib.so (include/sib.h). One long handle = the executor's sib_engine, or (cfg[9] = 1) its sib_client
+ * view of the engine shared by the bolts of this worker JVM.
  * NOT COMPILED in this repository's CI: there is no JDK on the build or GPU boxes. Every method maps 1:1 to a
  * C entry point; csrc/sib_jni.cpp holds the Java_dke_model_NativeInfer_* shims (built when jni.h is present).
  */
@@ -10,7 +11,8 @@ public final class NativeInfer {
 
     private NativeInfer() {}
 
-    /** sib_engine_open. cfg = {device, taskIndex, maxBatch, deadlineUs, precision, nSlots, guard}; returns handle. */
+    /** sib_engine_open / sib_client_open. cfg = {device, taskIndex, maxBatch, deadlineUs, precision, nSlots, guard,
+     *  jsonOnGpu, strictBatching, shared} (shorter arrays take defaults for the rest); returns handle, 0 on failure. */
     public static native long open(byte[] modelBlob, int[] cfg, float guardTau);
     public static native void close(long engine);
     /** sib_submit_json on the tuple's UTF-8 bytes: returns N (>0), or SIB_EJSON(-1) / SIB_ESHAPE(-2) / SIB_EAGAIN(-4). */
