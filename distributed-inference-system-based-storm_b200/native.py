@@ -218,7 +218,7 @@ class Engine:
         self._h = C.c_void_p()
         self._blob = blob
         cfg = Config(device, task_index, max_batch, deadline_us, precision, n_slots, 1 if guard else 0, guard_tau,
-                     1 if json_on_gpu else 0, 1 if strict_batching else 0)
+                     int(json_on_gpu), 1 if strict_batching else 0)
         rc = lib.sib_engine_open(blob, len(blob), C.byref(cfg), C.byref(self._h))
         if rc:
             raise SibError(rc, "sib_engine_open")

@@ -56,7 +56,9 @@ typedef struct sib_config {
                             instance per tuple, canonical nesting); tuples it cannot take are re-read by the host
                             decoder when their batch completes, so results are the same either way. In this mode a
                             malformed or wrong-shaped tuple is reported in sib_result.status (SIB_EJSON / SIB_ESHAPE,
-                            n = 0) instead of by sib_submit_json's return value. (default 0) */
+                            n = 0) instead of by sib_submit_json's return value. 2 = auto: an idle engine decodes on
+                            the submitting thread (lowest single-tuple latency), a busy one ships the text (highest
+                            rate); a bad tuple is then reported one way or the other. (default 0) */
     int32_t strict_batching; /* 0 (default): a tuple that finds no batch queued or in flight is launched as soon as it
                             is written, so at low arrival rates nobody sits out deadline_us, and under load batches
                             fill while the previous one runs (p50 45 us instead of 215 us at 10 k tuples/s, 132 us

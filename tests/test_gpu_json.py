@@ -138,3 +138,26 @@ def test_gpu_decode_full_rate(sib, presets):
         assert r["completed"] == 20000 and r["rejected"] == 0
         st = e.stats()
         assert st.images == 20000 and st.json_gpu_decoded == 20000 and st.json_host_redone == 0
+
+
+def test_auto_decode_uses_both_decoders_and_gives_the_same_bits(sib, presets):
+    """json_on_gpu = 2: a tuple that finds the engine idle is decoded on the submitting thread, one that finds it
+    busy is shipped as text; predictions do not depend on which (both decoders are bit-exact with each other)."""
+    m = presets["mnist-lenet5"]
+    ms = sib.modelspec
+    x = ms.synthetic_images(m, 84, 300)
+    payloads = [ms.instances_json(x[i:i + 1]) for i in range(300)]
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=500) as h:
+        want, _, _ = h.forward_sync(x)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=500, json_on_gpu=2) as e:
+        got = []
+        for i, p in enumerate(payloads):                  # a burst: the first is alone, the rest arrive on a busy engine
+            while e.submit_json(i, p) == sib.native.EAGAIN:
+                got += e.poll(timeout_us=1000)
+        e.flush()
+        while len(got) < 300:
+            got += e.poll(timeout_us=100000)
+        st = e.stats()
+    assert [g[0] for g in got] == list(range(300))
+    assert np.concatenate([g[1] for g in got]).tobytes() == want.tobytes()
+    assert 0 < st.json_gpu_decoded < 300                  # some went each way

@@ -14,7 +14,8 @@ js = [sib.modelspec.instances_json(x[i:i + 1]) for i in range(64)]
 N = 3000
 for name, kw, submit in (("T1 sib_submit_f32", {}, lambda e, i: e.submit_f32(i, x[i % 64:i % 64 + 1])),
                          ("T2 sib_submit_json host decode", {}, lambda e, i: e.submit_json(i, js[i % 64])),
-                         ("T2 sib_submit_json gpu decode", {"json_on_gpu": True}, lambda e, i: e.submit_json(i, js[i % 64]))):
+                         ("T2 sib_submit_json gpu decode", {"json_on_gpu": 1}, lambda e, i: e.submit_json(i, js[i % 64])),
+                         ("T2 sib_submit_json auto decode", {"json_on_gpu": 2}, lambda e, i: e.submit_json(i, js[i % 64]))):
     with sib.native.Engine(blob, max_batch=64, deadline_us=200, **kw) as e:
         lat = []
         for i in range(N + 200):

@@ -12,7 +12,8 @@ blob = m.to_blob()
 x = sib.modelspec.synthetic_images(m, 5, 256)
 f32 = [np.ascontiguousarray(x[i:i + 1]) for i in range(256)]
 js = [sib.modelspec.instances_json(x[i:i + 1]) for i in range(64)]
-for mode, payloads, name, gpu_json in ((sib.native.LG_F32, f32, "T1 f32 tuple", False), (sib.native.LG_JSON, js, "T2 json tuple (gpu decode)", True)):
+for mode, payloads, name, gpu_json in ((sib.native.LG_F32, f32, "T1 f32 tuple", False), (sib.native.LG_JSON, js, "T2 json tuple (gpu decode)", 1),
+                                     (sib.native.LG_JSON, js, "T2 json tuple (auto decode)", 2)):
     for producers in (2, 4, 8):
         with sib.native.Engine(blob, max_batch=4096, deadline_us=200, n_slots=6, json_on_gpu=gpu_json) as e:
             sib.native.loadgen(e, payloads, 50000.0, 5000, mode=mode, producers=producers)
