@@ -77,6 +77,8 @@ struct Slot {
     float* h_probs = nullptr;    // pinned, max_batch x ncls
     int32_t* h_argmax = nullptr; // pinned
     int32_t* h_guard_n = nullptr; // pinned, 1
+    int32_t* r_argmax = nullptr;  // where the last launch's argmax / guard count landed (inside the h_probs block)
+    int32_t* r_guard_n = nullptr;
     DevBufs dev;
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
@@ -141,7 +143,8 @@ int sib_engine::alloc_dev(DevBufs& d, bool with_io) {
     const size_t mb = (size_t)cfg.max_batch, nc = model.n_classes;
     if (with_io) {
         CU_TRY(cudaMalloc((void**)&d.d_in, mb * model.img_elems * sizeof(float)));
-        CU_TRY(cudaMalloc((void**)&d.d_probs, mb * nc * sizeof(float)));
+        // room for the packed result block of a launch: probs[n][nc] | argmax[n] | guard count (one D2H copy)
+        CU_TRY(cudaMalloc((void**)&d.d_probs, (mb * (nc + 1) + 4) * sizeof(float)));
         CU_TRY(cudaMalloc((void**)&d.d_logits, mb * nc * sizeof(float)));
         CU_TRY(cudaMalloc((void**)&d.d_argmax, mb * sizeof(int32_t)));
     }
@@ -163,10 +166,12 @@ void sib_engine::free_dev(DevBufs& d) {
 int sib_engine::alloc_slot(Slot& s) {
     const size_t mb = (size_t)cfg.max_batch, nc = model.n_classes;
     CU_TRY(cudaHostAlloc((void**)&s.h_in, mb * model.img_elems * sizeof(float), cudaHostAllocDefault));
-    CU_TRY(cudaHostAlloc((void**)&s.h_probs, mb * nc * sizeof(float), cudaHostAllocDefault));
+    CU_TRY(cudaHostAlloc((void**)&s.h_probs, (mb * (nc + 1) + 4) * sizeof(float), cudaHostAllocDefault));
     CU_TRY(cudaHostAlloc((void**)&s.h_argmax, mb * sizeof(int32_t), cudaHostAllocDefault));
     CU_TRY(cudaHostAlloc((void**)&s.h_guard_n, 2 * sizeof(int32_t), cudaHostAllocDefault));
     s.h_guard_n[0] = 0;
+    s.r_argmax = s.h_argmax;
+    s.r_guard_n = s.h_guard_n;
     int r = alloc_dev(s.dev, true);
     if (r) return r;
     if (cfg.json_on_gpu) {
@@ -262,14 +267,18 @@ int sib_engine::launch_locked(int si) {
         }
         chk(cudaMemcpyAsync(s.h_tflags, s.d_tflags, (size_t)s.n_text * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H text flags");
     }
-    if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
-    chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)s.images * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream), "D2H probs");
-    chk(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)s.images * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H argmax");
-    size_t d2h = (size_t)s.images * (nc * sizeof(float) + sizeof(int32_t));
-    if (cfg.precision != SIB_PREC_FP32 && cfg.guard) {
-        chk(cudaMemcpyAsync(s.h_guard_n, s.dev.guard.d_count, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H guard count");
-        d2h += sizeof(int32_t);
-    }
+    // Results of this launch are packed behind one another on the device -- probs[n][nc] | argmax[n] | guard count --
+    // so that they come home in one copy (three small D2H copies were a fifth of a single tuple's round trip).
+    const size_t n_img = (size_t)s.images;
+    int32_t* d_arg = reinterpret_cast<int32_t*>(s.dev.d_probs + n_img * nc);
+    GuardScratch g = s.dev.guard;
+    g.d_count = d_arg + n_img;
+    const bool guarded = cfg.precision != SIB_PREC_FP32 && cfg.guard;
+    if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, d_arg, &g, s.stream);
+    const size_t d2h = (n_img * (nc + 1) + (guarded ? 1 : 0)) * sizeof(float);
+    chk(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, d2h, cudaMemcpyDeviceToHost, s.stream), "D2H results");
+    s.r_argmax = reinterpret_cast<int32_t*>(s.h_probs + n_img * nc);
+    s.r_guard_n = s.r_argmax + n_img;
     chk(cudaEventRecord(s.done, s.stream), "event record");
     s.status = rc;
     s.state = Slot::INFLIGHT;
@@ -700,7 +709,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                     set_error(std::string("batch failed: ") + cudaGetErrorString(q));
                 }
                 s.state = Slot::READY;
-                if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.h_guard_n[0];
+                if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.r_guard_n[0];
                 if (s.n_text > 0) e->redo_flagged_locked(s);
             }
             while (got < max && s.next_entry < s.entries.size()) {
@@ -710,7 +719,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                 r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status != SIB_OK ? s.status : en.status; r.reserved = 0;
                 if (en.n == 0) { r.probs = nullptr; r.argmax = nullptr; }
                 else if (en.side >= 0) { r.probs = s.side[(size_t)en.side].probs.data(); r.argmax = s.side[(size_t)en.side].argmax.data(); }
-                else { r.probs = s.h_probs + (size_t)en.offset * nc; r.argmax = s.h_argmax + en.offset; }
+                else { r.probs = s.h_probs + (size_t)en.offset * nc; r.argmax = s.r_argmax + en.offset; }
             }
             if (s.next_entry == s.entries.size()) {
                 s.state = Slot::HANDED;
