@@ -61,7 +61,7 @@ typedef struct sib_config {
                             rate); a bad tuple is then reported one way or the other. (default 0) */
     int32_t strict_batching; /* 0 (default): a tuple that finds no batch queued or in flight is launched as soon as it
                             is written, so at low arrival rates nobody sits out deadline_us, and under load batches
-                            fill while the previous one runs (p50 45 us instead of 215 us at 10 k tuples/s, 132 us
+                            fill while the previous one runs (p50 39 us instead of 215 us at 10 k tuples/s, 115 us
                             instead of 265 us at 1 M tuples/s: profiles/latency_r01.jsonl). 1: batches are launched
                             by max_batch, deadline_us and sib_flush only. */
 } sib_config;
