@@ -56,6 +56,21 @@ inline int parse_number(Cur& c, float* out) {
     if (q < end && *q == '.') {
         q++;
         if (q >= end || (unsigned)(*q - '0') > 9u) return SIB_EJSON;
+        // Eight fraction digits at a time (a pixel is typically 0.dddddddd): one 64-bit load, a mask test for "all
+        // digits", three multiplies. nd may over-count leading zeros here; that can only send a number to the slow
+        // path, which is correctly rounded as well, so the result is the same either way.
+        while (end - q >= 8 && nd + 8 <= 18) {
+            uint64_t v;
+            std::memcpy(&v, q, 8);
+            if ((((v & 0xF0F0F0F0F0F0F0F0ull) | (((v + 0x0606060606060606ull) & 0xF0F0F0F0F0F0F0F0ull) >> 4)) != 0x3333333333333333ull)) break;
+            v -= 0x3030303030303030ull;
+            v = (v * 10) + (v >> 8);
+            v = (((v & 0x000000FF000000FFull) * (100ull + (1000000ull << 32))) + (((v >> 16) & 0x000000FF000000FFull) * (1ull + (10000ull << 32)))) >> 32;
+            if (mant != 0 || v != 0) nd += 8;
+            mant = mant * 100000000ull + v;
+            e10 -= 8;
+            q += 8;
+        }
         while (q < end && (unsigned)(*q - '0') <= 9u) {
             if (nd < 18) {
                 unsigned d = (unsigned)(*q - '0');
