@@ -48,8 +48,14 @@ namespace {
 #ifndef SIB_CONV1_UMMA
 #define SIB_CONV1_UMMA 0   // 1: conv1 on tcgen05.mma with operands in TMEM (sib_tc_conv1_umma.cuh)
 #endif
+#ifndef SIB_CONV2_UMMA
+#define SIB_CONV2_UMMA (SIB_CONV1_UMMA ? 0 : 1)   // 1: conv2 on tcgen05.mma, A rows and accumulators in TMEM (sib_tc_conv2_umma.cuh)
+#endif
+#if SIB_CONV1_UMMA && SIB_CONV2_UMMA
+#error "the tcgen05 variants of conv1 and conv2 each use the whole TMEM: pick one"
+#endif
 #ifndef SIB_CONV1_WARPS
-#define SIB_CONV1_WARPS (SIB_CONV1_UMMA ? 8 : 12)
+#define SIB_CONV1_WARPS (SIB_CONV1_UMMA ? 8 : SIB_CONV2_UMMA ? 11 : 12)
 #endif
 #ifndef SIB_BATCH_ROWS
 #define SIB_BATCH_ROWS 2
@@ -93,11 +99,14 @@ constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #ifndef SIB_TAIL_FIRST
 #define SIB_TAIL_FIRST 0     // 1: conv2 and fc warps get the lowest warp ids (they are the oldest warps of their sub-partition)
 #endif
+#ifndef SIB_DIAG_SKIP
+#define SIB_DIAG_SKIP 0      // diagnostic builds only (results are wrong): 1 = conv1 warps only keep the slot protocol going, 2 = the same for the dense head, 3 = both
+#endif
 #ifndef SIB_FC_IN_CONV2
 #define SIB_FC_IN_CONV2 0   // 1: no fc warp; conv2 warp (pair % kConv2Warps) runs the dense head of a pair after its tiles
 #endif
 constexpr int kFcWarps = SIB_FC_IN_CONV2 ? 0 : 1;
-constexpr int kIssueWarps = SIB_CONV1_UMMA ? 2 : 0;  // tcgen05.mma issuers (conv1 warps = two teams of 4)
+constexpr int kIssueWarps = SIB_CONV1_UMMA ? 2 : SIB_CONV2_UMMA ? 1 : 0;  // tcgen05.mma issuers
 constexpr int kWarps = kConv1Warps + kConv2Warps + kFcWarps + kIssueWarps;
 constexpr int kThreadsTc = kWarps * 32;
 constexpr int kG = 8;     // images per ring slot (conv stages)
@@ -126,7 +135,12 @@ struct Net {
     static constexpr int P1_BUF = kG * P1_IMG + 16;                 // + slack for the K-padding over-read
     static constexpr int NB1 = 3;                                   // p1 ring slots
     static constexpr int P2_STRIDE = FEAT + 8;                      // halves; +8 keeps A-fragment loads conflict-free
-    static constexpr int P2_BUF = kPair * P2_STRIDE;
+    // tcgen05 dense head: p2 / h1 / h2 are B operands (K-major, no swizzle: [img/8][k/8][img%8][k%8]), the weights A operands
+    // ([m/8][k/8][m%8][k%8]); *_SBO = bytes between 8-row groups, 128 bytes between K chunks
+    static constexpr int F1_SBO = FEAT / 8 * 128, F2_SBO = 128 / 8 * 128, F3_SBO = 96 / 8 * 128;
+    static constexpr int F1_GROUPS = 15, F2_GROUPS = 11, F3_GROUPS = 2;   // row groups that are stored (120 | 84 -> 88 | 10 -> 16 rows)
+    static constexpr int P2_BUF = SIB_CONV2_UMMA ? kPair * FEAT : kPair * P2_STRIDE;
+    static constexpr int DBG_P2 = kPair * P2_STRIDE;               // the stage dump keeps the padded [img][feature] layout
     static constexpr int H1_STRIDE = 136, H2_STRIDE = 104;
     // Input staging. H % 8 == 0: two register batches of 4 rows (2 scoreboard slots, no shared-memory cost).
     // Otherwise: a cp.async ring of PD rows per warp (in-order groups, costs ~10 shared-memory wavefronts a row).
@@ -141,29 +155,36 @@ struct Net {
     static constexpr int W_C2 = W_C1 + 2 * 5 * 64;               // [5 kh][2 ks][2 nt][32][2]
     static constexpr int NT1 = 15;                               // fc1 N tiles: 120 outputs, no padding tile
     static constexpr int W_F1 = W_C2 + 5 * 2 * 2 * 64;           // [KS1][NT1][32][2]
-    static constexpr int W_F2 = W_F1 + KS1 * NT1 * 64;           // [8 ks][12 nt][32][2]
-    static constexpr int W_F3 = W_F2 + 8 * 12 * 64;              // [6 ks][2 nt][32][2]
-    static constexpr int W_BIAS = W_F3 + 6 * 2 * 64;             // fp32: c1[8] c2[16] f1[128] f2[96] f3[16]
+    static constexpr int W_F2 = W_F1 + (SIB_CONV2_UMMA ? F1_GROUPS * F1_SBO / 4 : KS1 * NT1 * 64);  // [8 ks][12 nt][32][2]
+    static constexpr int W_F3 = W_F2 + (SIB_CONV2_UMMA ? F2_GROUPS * F2_SBO / 4 : 8 * 12 * 64);     // [6 ks][2 nt][32][2]
+    static constexpr int W_BIAS = W_F3 + (SIB_CONV2_UMMA ? F3_GROUPS * F3_SBO / 4 : 6 * 2 * 64);    // fp32: c1[8] c2[16] f1[128] f2[96] f3[16]
     static constexpr int W_C1U = W_BIAS + 8 + 16 + 128 + 96 + 16;  // conv1 as tcgen05 B operands: [even|odd][5 kh][16 n][16 k] halves
-    static constexpr int W_TOTAL = W_C1U + 2 * 5 * 128;
+    // conv2 as tcgen05 B operands: per K step the kernel rows 4,3,2,1,0 and a block of zeros stacked along N (96 x 16 halves)
+    static constexpr int B2U_KS_BYTES = 6 * 512;
+    static constexpr int W_C2U = W_C1U + 2 * 5 * 128;
+    static constexpr int W_TOTAL = W_C2U + 2 * B2U_KS_BYTES / 4;
     // shared memory map (bytes)
     static constexpr int S_FCW = 0;                                        // fc1|fc2|fc3 fragments
     static constexpr int S_FCW_BYTES = (W_BIAS - W_F1) * 4;
     static constexpr int S_BIAS = S_FCW + S_FCW_BYTES;                     // 264 floats
     static constexpr int S_B1U = ((S_BIAS + 264 * 4 + 127) / 128) * 128;   // conv1 B operands for tcgen05 (5 KB)
-    static constexpr int S_P1 = SIB_CONV1_UMMA ? S_B1U + 2 * 5 * 512 : S_BIAS + 264 * 4;
+    static constexpr int S_B2U = S_B1U;                                    // conv2 B operands for tcgen05 (5 KB); one variant at a time
+    static constexpr int S_P1 = SIB_CONV2_UMMA ? S_B2U + 2 * B2U_KS_BYTES : SIB_CONV1_UMMA ? S_B1U + 2 * 5 * 512 : S_BIAS + 264 * 4;
     static constexpr int S_P2 = S_P1 + NB1 * P1_BUF * 2;
     static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
     static constexpr int NHB = SIB_FC_IN_CONV2 ? 2 : 1;                    // h1/h2 buffers: dense heads of two pairs may overlap
-    static constexpr int S_H2 = S_H1 + NHB * kPair * H1_STRIDE * 2;
-    static constexpr int S_RING = S_H2 + NHB * kPair * H2_STRIDE * 2;
+    static constexpr int S_H2 = S_H1 + (SIB_CONV2_UMMA ? 2 * F2_SBO : NHB * kPair * H1_STRIDE * 2);
+    static constexpr int S_FCS = S_H2 + (SIB_CONV2_UMMA ? 2 * F3_SBO : NHB * kPair * H2_STRIDE * 2);  // tcgen05 head: logits [16][10] fp32, lane <-> image transpose
+    static constexpr int S_RING = S_FCS + (SIB_CONV2_UMMA ? kPair * 10 * 4 : 0);
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
     static constexpr int URING_ROW = 2 * W * C + 16;                       // halves: Umma<N>::UROW
     static constexpr int S_STAGE = S_RING + kConv1Warps * 2 * (SIB_CONV1_UMMA ? URING_ROW : RING_ROW) * 2; // cp.async landing zone
     static constexpr int S_BAR = ((S_STAGE + ((REG_STAGE || SIB_CONV1_UMMA) ? 0 : kConv1Warps * PD * STAGE_ROW) + 7) / 8) * 8;
     static constexpr int B_P1F = 0, B_P1E = NB1, B_P2F = 2 * NB1, B_P2E = 2 * NB1 + 2;
     static constexpr int B_UA = 2 * NB1 + 4, B_UDF = B_UA + 16, B_UDE = B_UDF + 8;  // tcgen05 conv1: a_full[8] a_free[8], d_full[4] (+4 unused), d_empty[4] (+4 unused)
-    static constexpr int B_FCW = SIB_CONV1_UMMA ? B_UDE + 8 : 2 * NB1 + 4;  // fc weight image has landed (bulk copy)
+    static constexpr int B_U2 = 2 * NB1 + 4;                               // tcgen05 conv2: a_full[16] a_free[16] d_full[8] d_empty[8]
+    static constexpr int B_FC = B_U2 + 48;                                 // tcgen05 dense head: f_full[3] h1_full h2_full
+    static constexpr int B_FCW = SIB_CONV1_UMMA ? B_UDE + 8 : SIB_CONV2_UMMA ? B_FC + 5 : 2 * NB1 + 4;  // fc weight image has landed (bulk copy)
     static constexpr int N_BAR = B_FCW + 1;
     static constexpr int S_TMEM = S_BAR + N_BAR * 8;                       // TMEM base address handed out by tcgen05.alloc
     static constexpr int S_TOTAL = S_TMEM + 8;
@@ -260,9 +281,15 @@ struct TcParams {
     float* dbg;      // may be null: CTA 0 dumps p1/p2/h1/h2 of its first 16 images (tests)
 };
 
-#if SIB_CONV1_UMMA
+#if SIB_CONV1_UMMA || SIB_CONV2_UMMA
 #include "sib_tc_umma.cuh"
+#endif
+#if SIB_CONV1_UMMA
 #include "sib_tc_conv1_umma.cuh"
+#endif
+#if SIB_CONV2_UMMA
+#include "sib_tc_conv2_umma.cuh"
+#include "sib_tc_fc_umma.cuh"
 #endif
 
 // ---- conv1 role (mma.sync form) ------------------------------------------------------------------------------
@@ -348,7 +375,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         // A span whose first column already lies past the last image has nothing to compute (the tail of a batch:
         // with 1 image in a launch, 13 of the pair's 14 spans). It only keeps the slot protocol going. Image indices
         // grow with gs, so every later span of this warp is empty as well and the prefetch state no longer matters.
-        if (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= P.n) {
+        if ((SIB_DIAG_SKIP & 1) || (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= P.n)) {
             mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
             mbar_arrive(&p1_full[buf]);
             gs = n_gs; valid = n_valid; src = n_src; img0 = n_img0;
@@ -650,6 +677,7 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
         mbar_wait(&p2_full[buf], use & 1);
         mbar_wait(bars + N::B_FCW, 0);  // the weight image is in (completes once; later waits fall through)
+        if (SIB_DIAG_SKIP & 2) { mbar_arrive(&p2_empty[buf]); return; }
         // ---- fc1: [16 x FEAT] . [FEAT x 120]: 15 N tiles = 15 independent accumulator chains
         // (h1 columns 120..127 stay zero from the set-up; fc2's K padding multiplies them by zero weights)
         {
@@ -679,7 +707,7 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
                 *reinterpret_cast<uint32_t*>(h1 + g * N::H1_STRIDE + n0) = Ops<T>::pack(v0, v1);
                 *reinterpret_cast<uint32_t*>(h1 + (g + 8) * N::H1_STRIDE + n0) = Ops<T>::pack(v2, v3);
                 if (dump) {
-                    float* d = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + N::P2_BUF;
+                    float* d = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + N::DBG_P2;
                     d[g * 128 + n0] = v0; d[g * 128 + n0 + 1] = v1; d[(g + 8) * 128 + n0] = v2; d[(g + 8) * 128 + n0 + 1] = v3;
                 }
             }
@@ -794,6 +822,16 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
     for (int Qi = 0; (int)(blockIdx.x + Qi * gridDim.x) < nPairs; Qi++) fc_pair<N, T, DBG>(P, smem, lane, Qi);
 }
 
+// arrivals per p1 slot on p1_empty / p2_full
+template <typename N>
+__host__ __device__ constexpr int kConv2Arrivals() {
+#if SIB_CONV2_UMMA
+    return U2<N>::NWORK * 32;
+#else
+    return N::TILES2 * 32;
+#endif
+}
+
 template <typename N, typename T, bool DBG>
 __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -818,10 +856,31 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
         __syncwarp();
         if (warp == 0) tmem_alloc_all(reinterpret_cast<uint32_t*>(smem + N::S_TMEM));
 #endif
+#if SIB_CONV2_UMMA
+        {
+            const uint4* bs = reinterpret_cast<const uint4*>(P.wpack + N::W_C2U);
+            uint4* bd = reinterpret_cast<uint4*>(smem + N::S_B2U);
+            for (int i = threadIdx.x; i < 2 * N::B2U_KS_BYTES / 16; i += blockDim.x) bd[i] = bs[i];
+        }
+        __syncwarp();
+        if (warp == 0) tmem_alloc_all(reinterpret_cast<uint32_t*>(smem + N::S_TMEM));
+#endif
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-#if !SIB_CONV1_UMMA
+#if !SIB_CONV1_UMMA && !SIB_CONV2_UMMA
             *reinterpret_cast<uint32_t*>(smem + N::S_TMEM) = 0u;  // mma.sync build: the conv1 span counter lives here
+#endif
+#if SIB_CONV2_UMMA
+            {
+                using U = U2<N>;
+                for (int i = 0; i < U::NA; i++) mbar_init(&bars[N::B_U2 + i], U::NWORK * 32);                   // a_full : every lane of every worker
+                for (int i = 0; i < U::NA; i++) mbar_init(&bars[N::B_U2 + U::NA + i], 1);                       // a_free : one tcgen05.commit
+                for (int i = 0; i < U::NDP; i++) mbar_init(&bars[N::B_U2 + 2 * U::NA + i], 1);                  // d_full : one tcgen05.commit
+                for (int i = 0; i < U::NDP; i++) mbar_init(&bars[N::B_U2 + 2 * U::NA + U::NDP + i], U::NWORK * 32);  // d_empty: every lane of every worker
+                for (int i = 0; i < 3; i++) mbar_init(&bars[N::B_FC + i], 1);  // f_full: fc1 | fc2 | fc3 mma retired (one tcgen05.commit)
+                mbar_init(&bars[N::B_FC + 3], 4 * 32);                         // h1_full: the four lane quadrants' warps
+                mbar_init(&bars[N::B_FC + 4], 3 * 32);                         // h2_full: quadrants 0..2 (84 -> 96 features)
+            }
 #endif
 #if SIB_CONV1_UMMA
             for (int i = 0; i < 8; i++) mbar_init(&bars[N::B_UA + i], 128);     // a_full : every thread of the team that owns the pair
@@ -831,11 +890,11 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
 #endif
             for (int i = 0; i < N::NB1; i++) {
                 mbar_init(&bars[N::B_P1F + i], SIB_CONV1_UMMA ? 256 : N::SPANS * 32);  // p1_full : every conv1 lane working on the slot
-                mbar_init(&bars[N::B_P1E + i], N::TILES2 * 32);       // p1_empty: every lane of every conv2 tile
+                mbar_init(&bars[N::B_P1E + i], kConv2Arrivals<N>());  // p1_empty: every lane of every conv2 tile | worker
             }
             for (int i = 0; i < 2; i++) {
-                mbar_init(&bars[N::B_P2F + i], 2 * N::TILES2 * 32);   // p2_full : two slots of conv2 tiles
-                mbar_init(&bars[N::B_P2E + i], 32);                   // p2_empty: every lane of the warp that runs the pair's dense head
+                mbar_init(&bars[N::B_P2F + i], 2 * kConv2Arrivals<N>());  // p2_full : two slots of conv2 tiles | workers
+                mbar_init(&bars[N::B_P2E + i], SIB_CONV2_UMMA ? 1 : 32);  // p2_empty: every lane of the warp that runs the pair's dense head | fc1's tcgen05.commit
             }
             mbar_init(&bars[N::B_FCW], 1);
 #if SIB_TMA_WEIGHTS
@@ -867,6 +926,21 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     else if (warp < kConv1Warps + kConv2Warps) { if (SIB_ROLE_MASK & 2) conv2_role<N, T, DBG>(P, smem, warp - kConv1Warps, lane); }
     else if (warp < kConv1Warps + kConv2Warps + kFcWarps) { if (SIB_ROLE_MASK & 4) fc_role<N, T, DBG>(P, smem, lane); }
     else if (SIB_ROLE_MASK & 8) conv1u_issuer<N, T>(P, smem, warp - kConv1Warps - kConv2Warps - kFcWarps, tmem);
+    tc5_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_free_all(tmem);
+#elif SIB_CONV2_UMMA
+    tc5_fence_before();
+    __syncthreads();
+    tc5_fence_after();
+    const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + N::S_TMEM);
+    // warps: conv1 x kConv1Warps | issuer | conv2 workers (hardware warp 4k + q = TMEM lane quadrant q) | fc
+    static_assert((kConv1Warps + kIssueWarps) % 4 == 0 && kConv2Warps == 3 && kFcWarps == 1 && !SIB_TAIL_FIRST && !SIB_FC_IN_CONV2 && !SIB_DYN_SPANS,
+                  "tcgen05 conv2: conv2 worker q must sit on hardware warp 4k + q (its TMEM lane quadrant)");
+    if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
+    else if (warp < kConv1Warps + kIssueWarps) conv2u_issuer<N, T>(P, smem, tmem);
+    else if (warp < kConv1Warps + kIssueWarps + kConv2Warps) conv2u_worker<N, T, DBG>(P, smem, warp - kConv1Warps - kIssueWarps, lane, tmem);
+    else fcu_head<N, T, DBG>(P, smem, lane, tmem);
     tc5_fence_before();
     __syncthreads();
     if (warp == 0) tmem_free_all(tmem);
@@ -933,9 +1007,25 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
                     return (i < (int)D.a && j < (int)D.b) ? k[i * D.b + j] : 0.f;
                 });
     };
+#if SIB_CONV2_UMMA
+    // tcgen05 A operands: the TRANSPOSED dense kernels (row m = output feature), K-major, no swizzle
+    auto dense_a = [&](int off, int groups, int sbo, const LayerDesc& D) {
+        const float* k = wt + D.w_off;  // [in][out]
+        uint16_t* dst = reinterpret_cast<uint16_t*>(&w[off]);
+        for (int m = 0; m < groups * 8; m++)
+            for (int i = 0; i < sbo / 16; i++) {
+                const float x = (m < (int)D.b && i < (int)D.a) ? k[i * D.b + m] : 0.f;
+                dst[(m / 8) * (sbo / 2) + (i / 8) * 64 + (m % 8) * 8 + (i % 8)] = Ops<T>::host_bits(x);
+            }
+    };
+    dense_a(N::W_F1, N::F1_GROUPS, N::F1_SBO, L[2]);
+    dense_a(N::W_F2, N::F2_GROUPS, N::F2_SBO, L[3]);
+    dense_a(N::W_F3, N::F3_GROUPS, N::F3_SBO, L[4]);
+#else
     dense(N::W_F1, N::KS1, N::NT1, L[2]);
     dense(N::W_F2, 8, 12, L[3]);
     dense(N::W_F3, 6, 2, L[4]);
+#endif
     // conv1 as tcgen05 B operands: canonical K-major no-swizzle tiles [n/8][k/8][n%8][k%8] of halves
     for (int v = 0; v < 2; v++)
         for (int kh = 0; kh < 5; kh++) {
@@ -947,6 +1037,18 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
                     dst[(n / 8) * 128 + (k / 8) * 64 + (n % 8) * 8 + (k % 8)] = Ops<T>::host_bits(x);
                 }
         }
+    // conv2 as tcgen05 B operands: per K step, blocks of 16 rows (= output channels) for the kernel rows 4,3,2,1,0, then
+    // 16 rows of zeros; k = kw * 6 + c of that kernel row (sib_tc_conv2_umma.cuh: the issuer's N = 32 windows)
+    for (int ks = 0; ks < 2; ks++) {
+        uint16_t* dst = reinterpret_cast<uint16_t*>(&w[N::W_C2U + ks * N::B2U_KS_BYTES / 4]);
+        for (int blk = 0; blk < 5; blk++)
+            for (int nn = 0; nn < 16; nn++)
+                for (int k = 0; k < 16; k++) {
+                    const int kh = 4 - blk, n = blk * 16 + nn, j = ks * 16 + k;
+                    const float x = j >= 5 * N::C1 ? 0.f : f2[((kh * 5 + j / N::C1) * N::C1 + j % N::C1) * N::C2 + nn];
+                    dst[(n / 8) * 128 + (k / 8) * 64 + (n % 8) * 8 + (k % 8)] = Ops<T>::host_bits(x);
+                }
+    }
     float* b = reinterpret_cast<float*>(&w[N::W_BIAS]);
     std::memcpy(b, wt + L[0].b_off, 6 * 4);
     std::memcpy(b + 8, wt + L[1].b_off, 16 * 4);
@@ -1007,8 +1109,8 @@ void tc_release(TcWeights* w) {
 }
 
 size_t tc_debug_floats(int preset) {
-    return preset == 0 ? 2 * kG * NetMnist::PH1 * NetMnist::P1_ROW + NetMnist::P2_BUF + 16 * 128
-                       : 2 * kG * NetCifar::PH1 * NetCifar::P1_ROW + NetCifar::P2_BUF + 16 * 128;
+    return preset == 0 ? 2 * kG * NetMnist::PH1 * NetMnist::P1_ROW + NetMnist::DBG_P2 + 16 * 128
+                       : 2 * kG * NetCifar::PH1 * NetCifar::P1_ROW + NetCifar::DBG_P2 + 16 * 128;
 }
 
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
