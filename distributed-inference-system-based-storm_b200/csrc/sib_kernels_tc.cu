@@ -55,7 +55,7 @@ namespace {
 #error "the tcgen05 variants of conv1 and conv2 each use the whole TMEM: pick one"
 #endif
 #ifndef SIB_CONV1_WARPS
-#define SIB_CONV1_WARPS (SIB_CONV1_UMMA ? 8 : SIB_CONV2_UMMA ? 11 : 12)
+#define SIB_CONV1_WARPS (SIB_CONV1_UMMA ? 8 : 12)
 #endif
 #ifndef SIB_BATCH_ROWS
 #define SIB_BATCH_ROWS 2
@@ -69,7 +69,7 @@ namespace {
 constexpr int kConv1Warps = SIB_CONV1_WARPS;
 constexpr int kBR = SIB_BATCH_ROWS;  // rows per register prefetch batch (two batches in flight)
 #ifndef SIB_CONV2_WARPS
-#define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : 3)
+#define SIB_CONV2_WARPS (SIB_CONV1_UMMA ? 5 : SIB_CONV2_UMMA ? 6 : 3)   // tcgen05 conv2: two sets of three workers (TMEM lane quadrants 0..2)
 #endif
 constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #ifndef SIB_CONV1_PACK2
@@ -231,6 +231,7 @@ template <> struct Ops<__half> {
                      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
     }
     static uint16_t host_bits(float x) { return __half_as_ushort(__float2half_rn(x)); }
+    static float host_float(uint16_t b) { return __half2float(__ushort_as_half(b)); }
 };
 template <> struct Ops<__nv_bfloat16> {
     __device__ static __forceinline__ uint32_t pack(float lo, float hi) {
@@ -243,6 +244,7 @@ template <> struct Ops<__nv_bfloat16> {
                      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
     }
     static uint16_t host_bits(float x) { return __bfloat16_as_ushort(__float2bfloat16_rn(x)); }
+    static float host_float(uint16_t b) { return __bfloat162float(__ushort_as_bfloat16(b)); }
 };
 
 __device__ __forceinline__ uint32_t lds32(const uint16_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
@@ -826,7 +828,7 @@ __device__ __forceinline__ void fc_role(const TcParams& P, unsigned char* smem, 
 template <typename N>
 __host__ __device__ constexpr int kConv2Arrivals() {
 #if SIB_CONV2_UMMA
-    return U2<N>::NWORK * 32;
+    return U2<N>::NWORK * 32;  // one worker set
 #else
     return N::TILES2 * 32;
 #endif
@@ -893,7 +895,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
                 mbar_init(&bars[N::B_P1E + i], kConv2Arrivals<N>());  // p1_empty: every lane of every conv2 tile | worker
             }
             for (int i = 0; i < 2; i++) {
-                mbar_init(&bars[N::B_P2F + i], 2 * kConv2Arrivals<N>());  // p2_full : two slots of conv2 tiles | workers
+                mbar_init(&bars[N::B_P2F + i], (SIB_CONV2_UMMA ? 4 : 2) * kConv2Arrivals<N>());  // p2_full : two slots of conv2 tiles | both worker sets
                 mbar_init(&bars[N::B_P2E + i], SIB_CONV2_UMMA ? 1 : 32);  // p2_empty: every lane of the warp that runs the pair's dense head | fc1's tcgen05.commit
             }
             mbar_init(&bars[N::B_FCW], 1);
@@ -934,13 +936,21 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     __syncthreads();
     tc5_fence_after();
     const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem + N::S_TMEM);
-    // warps: conv1 x kConv1Warps | issuer | conv2 workers (hardware warp 4k + q = TMEM lane quadrant q) | fc
-    static_assert((kConv1Warps + kIssueWarps) % 4 == 0 && kConv2Warps == 3 && kFcWarps == 1 && !SIB_TAIL_FIRST && !SIB_FC_IN_CONV2 && !SIB_DYN_SPANS,
-                  "tcgen05 conv2: conv2 worker q must sit on hardware warp 4k + q (its TMEM lane quadrant)");
-    if (warp < kConv1Warps) conv1_role<N, T, DBG>(P, smem, warp, lane);
-    else if (warp < kConv1Warps + kIssueWarps) conv2u_issuer<N, T>(P, smem, tmem);
-    else if (warp < kConv1Warps + kIssueWarps + kConv2Warps) conv2u_worker<N, T, DBG>(P, smem, warp - kConv1Warps - kIssueWarps, lane, tmem);
-    else fcu_head<N, T, DBG>(P, smem, lane, tmem);
+    // 20 warps = 5 warpgroups: conv1 x 12 | workers set 0 (q 0..2), conv2 issuer | workers set 1 (q 0..2), dense head (q 3).
+    // A worker's / the head's TMEM lane quadrant is its hardware warp id mod 4. The launch gives every thread 96
+    // registers; the last two warpgroups hand theirs down to 64 and the conv1 warpgroups take 128 (setmaxnreg).
+    static_assert(kConv1Warps == 12 && kConv2Warps == 6 && kIssueWarps == 1 && kFcWarps == 1 && !SIB_TAIL_FIRST && !SIB_FC_IN_CONV2 && !SIB_DYN_SPANS,
+                  "tcgen05 conv2: warp layout");
+    if (warp < kConv1Warps) {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
+        conv1_role<N, T, DBG>(P, smem, warp, lane);
+    } else {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+        const int w = warp - kConv1Warps;  // 0..7
+        if ((w & 3) < 3) conv2u_worker<N, T, DBG>(P, smem, w & 3, w >> 2, lane, tmem);
+        else if (w == 3) conv2u_issuer<N, T>(P, smem, tmem);
+        else fcu_head<N, T, DBG>(P, smem, lane, tmem);
+    }
     tc5_fence_before();
     __syncthreads();
     if (warp == 0) tmem_free_all(tmem);
@@ -1045,7 +1055,13 @@ std::vector<uint32_t> pack_weights(const ModelDesc& m) {
             for (int nn = 0; nn < 16; nn++)
                 for (int k = 0; k < 16; k++) {
                     const int kh = 4 - blk, n = blk * 16 + nn, j = ks * 16 + k;
-                    const float x = j >= 5 * N::C1 ? 0.f : f2[((kh * 5 + j / N::C1) * N::C1 + j % N::C1) * N::C2 + nn];
+                    float x = j >= 5 * N::C1 ? 0.f : f2[((kh * 5 + j / N::C1) * N::C1 + j % N::C1) * N::C2 + nn];
+                    if (kh == 0 && j >= 30) {  // K slots 30, 31 meet the constant 1.0 of every A row: the bias, head and tail
+                        const float bv = wt[L[1].b_off + nn];
+                        const uint16_t hb = Ops<T>::host_bits(bv);
+                        const float hi = Ops<T>::host_float(hb);
+                        x = j == 30 ? hi : bv - hi;
+                    }
                     dst[(n / 8) * 128 + (k / 8) * 64 + (n % 8) * 8 + (k % 8)] = Ops<T>::host_bits(x);
                 }
     }

@@ -30,7 +30,8 @@ struct U2 {
     static constexpr int ROWS = N::PH1, OROWS = N::OH2, OP = N::PH2, RP = ROWS / 2;  // p1 rows, output rows, output pairs, p1 row pairs
     static constexpr int NA = 16, NDP = 8;                     // A row slots (ROWS used) / D row pairs resident in TMEM
     static constexpr int TM_A = 0, TM_D = ROWS * 16;
-    static_assert(NWORK <= kConv2Warps && ROWS <= NA && TM_D + NDP * 32 <= 512 && OROWS == 2 * OP && ROWS == OROWS + 4 && ROWS % 2 == 0 && RP == OP + 2, "conv2 umma tiling");
+    static constexpr int FC1_STEP = 3, FC2_STEP = RP - 1;      // worker steps that carry the previous pair's dense-head epilogues
+    static_assert(2 * NWORK <= kConv2Warps && ROWS <= NA && TM_D + NDP * 32 <= 512 && OROWS == 2 * OP && ROWS == OROWS + 4 && ROWS % 2 == 0 && RP == OP + 2, "conv2 umma tiling");
     static_assert(5 * N::C1 <= 32 && N::C2 == 16 && (N::OW2 % 2) == 0 && (N::P2_STRIDE * 2) % 16 == 0, "conv2 umma layout");
 };
 
@@ -65,6 +66,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&r)[32]) {
 }
 // D[tmem] (+)= A[tmem] . B[smem]^T with the B descriptor given as two words (the high word is the same for every tile)
 __device__ __forceinline__ void umma_ts2(uint32_t d, uint32_t a, uint32_t bdesc_lo, uint32_t bdesc_hi, uint32_t idesc, uint32_t accumulate) {
+    if (SIB_DIAG_SKIP & 8) return;  // diagnostic: everything but the tensor work
     asm volatile(
         "{\n\t.reg .pred p;\n\t.reg .b64 bd;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 bd, {%2, %3};\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], bd, %4, {%6, %6, %6, %6}, p;\n\t}\n" ::"r"(d), "r"(a), "r"(bdesc_lo),
@@ -128,15 +130,17 @@ __device__ __forceinline__ void fcu_epilogue(const TcParams& P, unsigned char* s
 // ---- worker warps: q = this warp's TMEM lane quadrant (hardware warp 4k + q) ------------------------------------------
 // Besides conv2 they run the dense head's epilogues for their quadrant (sib_tc_fc_umma.cuh): the head of pair Qi-1 is
 // computed while the first slot of pair Qi passes through here, so its two steps are slotted in after rows 4 and 9.
+// Two sets of workers share the row-pair steps of every tile: set s takes the steps rp with rp % 2 == s.
 template <typename N, typename T, bool DBG>
-__device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* smem, int q, int lane, uint32_t tmem) {
+__device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* smem, int q, int set, int lane, uint32_t tmem) {
     using U = U2<N>;
     const U2Bars<N> B(smem);
+    const bool fc1_mine = (U::FC1_STEP & 1) == set, fc2_mine = (U::FC2_STEP & 1) == set;
     const int nimg = max(0, min(U::IPQ, kG - q * U::IPQ));
     const int nlive = nimg * N::OW2;
     if (SIB_DIAG_SKIP & 4) {  // diagnostic: conv1 alone (the p1 slots are recycled unread)
         for (int lq = 0; conv2u_slot<N>(P, lq) >= 0; lq++) {
-            if (nimg == 0) continue;
+            if (nimg == 0 || set != 0) continue;
             mbar_wait_s(B.p1_full + (lq % N::NB1) * 8, (lq / N::NB1) & 1);
             mbar_arrive_s(B.p1_empty + (lq % N::NB1) * 8);
         }
@@ -145,8 +149,8 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
     if (nimg == 0) {  // no conv2 columns in this quadrant (mnist, q = 2): only the dense head's epilogues
         const int nPairs = (P.n + kPair - 1) / kPair;
         for (int Qi = 0; (int)(blockIdx.x + Qi * gridDim.x) < nPairs; Qi++) {
-            fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi);
-            fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi);
+            if (fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi);
+            if (fc2_mine) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi);
         }
         return;
     }
@@ -159,10 +163,9 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
     // p2 is the dense head's B operand: [img/8][k/8][img%8][k%8]; this lane's 8 channels are one 16-byte chunk of it
     const uint32_t offP2 = smem_u32(smem + N::S_P2) + ((ow >> 1) * 2 + odd) * 128 + imgl * 16;
     const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
-    const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS) + 8 + odd * 8;
-    float bias[8];
-#pragma unroll
-    for (int c = 0; c < 8; c++) bias[c] = biasp[c];
+    // The bias rides in the mma: K slots 30, 31 of every A row hold 1.0 and kernel row 0's B tile holds the bias there,
+    // split into a half-precision head and tail (b = hi + lo to ~22 bits); every output row meets kernel row 0 once.
+    const uint32_t ones = Ops<T>::pack(1.f, 1.f);
 
     int seq = 0;  // tiles that went through the tensor core so far
     int last = -1;
@@ -175,7 +178,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         mbar_wait_s(B.p1_full + buf1 * 8, use1 & 1);
         if ((lq & 1) == 0) mbar_wait_s(B.p2_empty + buf2 * 8, (use2 & 1) ^ 1);
         if (work == 0) {  // nothing to compute, keep the slot protocol going
-            mbar_arrive_s(B.p1_empty + buf1 * 8);
+            if (set == 0) mbar_arrive_s(B.p1_empty + buf1 * 8);
             mbar_arrive_s(B.p2_full + buf2 * 8);
             continue;
         }
@@ -189,33 +192,29 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         // issuer's step rp-1) starts its way out of TMEM; rows 2rp, 2rp+1 go in (32 LDS -> one tcgen05.st) under that
         // load's latency; then the pair's pool / bias / ReLU -> p2; the previous pair's dense head at two fixed steps.
 #pragma unroll 1
-        for (int rp = 0; rp <= U::RP; rp++) {
-            float dd[32];
-            int dp = 0;
-            if (rp >= 3) {
-                const int gq = seq * U::OP + rp - 3;
-                dp = gq & (U::NDP - 1);
-                mbar_wait_s(B.d_full + dp * 8, (gq / U::NDP) & 1);
-                tc5_fence_after();
-                tmem_ld32(tm_lane + U::TM_D + dp * 32, dd);
-            }
+        for (int rp = set; rp <= U::RP + 1; rp += 2) {  // rows in first: the issuer never waits for an epilogue
             if (rp < U::RP) {
                 mbar_wait_s(B.a_free + rp * 8, par ^ 1);  // the mma that read these row slots' previous tenants are done
                 tc5_fence_after();
                 const uint32_t src = src0 + rp * (2 * N::P1_ROW * 2);
                 uint32_t a[32];
 #pragma unroll
-                for (int k = 0; k < 16; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[k]) : "r"(src + k * 4));
+                for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[k]) : "r"(src + k * 4));
 #pragma unroll
-                for (int k = 0; k < 16; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[16 + k]) : "r"(src + N::P1_ROW * 2 + k * 4));
+                for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[16 + k]) : "r"(src + N::P1_ROW * 2 + k * 4));
+                a[15] = a[31] = ones;
                 tmem_st32(tm_lane + U::TM_A + rp * 32, a);
                 tmem_wait_st();
                 tc5_fence_before();
                 mbar_arrive_s(B.a_full + rp * 8);
                 if (rp == U::RP - 1) mbar_arrive_s(B.p1_empty + buf1 * 8);  // every row of the slot is in TMEM
             }
-            if (rp >= 3) {
-                const int j = rp - 3;
+            if (rp >= 4) {  // output pair rp-4 has been complete since the issuer's step rp-2: a whole step of slack
+                const int j = rp - 4, gq = seq * U::OP + j, dp = gq & (U::NDP - 1);
+                mbar_wait_s(B.d_full + dp * 8, (gq / U::NDP) & 1);
+                tc5_fence_after();
+                float dd[32];
+                tmem_ld32(tm_lane + U::TM_D + dp * 32, dd);
                 tmem_wait_ld();
                 tc5_fence_before();
                 mbar_arrive_s(B.d_empty + dp * 8);
@@ -224,7 +223,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
                 for (int c = 0; c < 8; c++) {
                     const float lo = fmaxf(dd[c], dd[16 + c]), hi = fmaxf(dd[c + 8], dd[24 + c]);
                     const float other = __shfl_xor_sync(0xffffffffu, odd ? lo : hi, 1);  // what the pair lane stores, it gets
-                    v[c] = fmaxf(fmaxf(odd ? hi : lo, other) + bias[c], 0.f);             // relu(max(.) + b) == max relu(. + b)
+                    v[c] = fmaxf(fmaxf(odd ? hi : lo, other), 0.f);                       // the bias is in already; relu(max(.)) == max relu(.)
                 }
                 if (live) {
                     uint4 pk;
@@ -239,8 +238,8 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
                 }
             }
             if ((lq & 1) == 0 && Qi > 0) {  // the previous pair's dense head
-                if (rp == 3) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
-                if (rp == U::RP - 1) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi - 1);
+                if (rp == U::FC1_STEP) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
+                if (rp == U::FC2_STEP) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi - 1);
             }
         }
         fence_proxy_async();  // p2 was written by ordinary stores and is read by the tensor core
@@ -249,8 +248,8 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         last = Qi;
     }
     if (last >= 0) {  // the last pair's dense head
-        fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, last);
-        fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, last);
+        if (fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, last);
+        if (fc2_mine) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, last);
     }
 }
 

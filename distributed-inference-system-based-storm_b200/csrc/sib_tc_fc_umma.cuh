@@ -20,6 +20,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint
 }
 // D[tmem] (+)= A[smem] . B[smem]^T ; issued by ONE elected lane of a converged warp
 __device__ __forceinline__ void umma_ss(uint32_t d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    if (SIB_DIAG_SKIP & 8) return;  // diagnostic: everything but the tensor work
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}\n" ::"r"(d), "l"(adesc), "l"(bdesc),
