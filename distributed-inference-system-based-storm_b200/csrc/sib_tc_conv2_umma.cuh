@@ -30,7 +30,6 @@ struct U2 {
     static constexpr int ROWS = N::PH1, OROWS = N::OH2, OP = N::PH2, RP = ROWS / 2;  // p1 rows, output rows, output pairs, p1 row pairs
     static constexpr int NA = 16, NDP = 8;                     // A row slots (ROWS used) / D row pairs resident in TMEM
     static constexpr int TM_A = 0, TM_D = ROWS * 16;
-    static constexpr int FC1_STEP = 3, FC2_STEP = RP - 1;      // worker steps that carry the previous pair's dense-head epilogues
     static_assert(2 * NWORK <= kConv2Warps && ROWS <= NA && TM_D + NDP * 32 <= 512 && OROWS == 2 * OP && ROWS == OROWS + 4 && ROWS % 2 == 0 && RP == OP + 2, "conv2 umma tiling");
     static_assert(5 * N::C1 <= 32 && N::C2 == 16 && (N::OW2 % 2) == 0 && (N::P2_STRIDE * 2) % 16 == 0, "conv2 umma layout");
 };
@@ -135,7 +134,7 @@ template <typename N, typename T, bool DBG>
 __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* smem, int q, int set, int lane, uint32_t tmem) {
     using U = U2<N>;
     const U2Bars<N> B(smem);
-    const bool fc1_mine = (U::FC1_STEP & 1) == set, fc2_mine = (U::FC2_STEP & 1) == set;
+    const bool fc1_mine = set == 1, fc2_mine = set == 0;  // which set runs the dense head's epilogues for this quadrant
     const int nimg = max(0, min(U::IPQ, kG - q * U::IPQ));
     const int nlive = nimg * N::OW2;
     if (SIB_DIAG_SKIP & 4) {  // diagnostic: conv1 alone (the p1 slots are recycled unread)
@@ -187,61 +186,59 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
         const uint32_t par = seq & 1;
 
-        // Row pairs, one loop body (the unrolled form was 36 KB of code; the kernel's roles together overflowed the
-        // instruction cache: 72% hit rate, profiles/ncu_tc_r02_notes.md). Step rp: output pair rp-3 (complete since the
-        // issuer's step rp-1) starts its way out of TMEM; rows 2rp, 2rp+1 go in (32 LDS -> one tcgen05.st) under that
-        // load's latency; then the pair's pool / bias / ReLU -> p2; the previous pair's dense head at two fixed steps.
+        // Rolled loops (the unrolled form was 36 KB of code; the kernel's roles together overflowed the instruction
+        // cache: 72% hit rate, profiles/ncu_tc_r02_notes.md). First this set's row pairs go into TMEM back to back, so
+        // the p1 slot returns to the conv1 warps as early as possible (they were waiting for it 20% of their time when
+        // rows and epilogues alternated); then the previous pair's fc1 epilogue, this set's output pairs, fc2's.
 #pragma unroll 1
-        for (int rp = set; rp <= U::RP + 1; rp += 2) {  // rows in first: the issuer never waits for an epilogue
-            if (rp < U::RP) {
-                mbar_wait_s(B.a_free + rp * 8, par ^ 1);  // the mma that read these row slots' previous tenants are done
-                tc5_fence_after();
-                const uint32_t src = src0 + rp * (2 * N::P1_ROW * 2);
-                uint32_t a[32];
+        for (int rp = set; rp < U::RP; rp += 2) {
+            mbar_wait_s(B.a_free + rp * 8, par ^ 1);  // the mma that read these row slots' previous tenants are done
+            tc5_fence_after();
+            const uint32_t src = src0 + rp * (2 * N::P1_ROW * 2);
+            uint32_t a[32];
 #pragma unroll
-                for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[k]) : "r"(src + k * 4));
+            for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[k]) : "r"(src + k * 4));
 #pragma unroll
-                for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[16 + k]) : "r"(src + N::P1_ROW * 2 + k * 4));
-                a[15] = a[31] = ones;
-                tmem_st32(tm_lane + U::TM_A + rp * 32, a);
-                tmem_wait_st();
-                tc5_fence_before();
-                mbar_arrive_s(B.a_full + rp * 8);
-                if (rp == U::RP - 1) mbar_arrive_s(B.p1_empty + buf1 * 8);  // every row of the slot is in TMEM
+            for (int k = 0; k < 15; k++) asm volatile("ld.shared.b32 %0, [%1];" : "=r"(a[16 + k]) : "r"(src + N::P1_ROW * 2 + k * 4));
+            a[15] = a[31] = ones;
+            tmem_st32(tm_lane + U::TM_A + rp * 32, a);
+            tmem_wait_st();
+            tc5_fence_before();
+            mbar_arrive_s(B.a_full + rp * 8);
+        }
+        if (((U::RP - 1) & 1) == set) mbar_arrive_s(B.p1_empty + buf1 * 8);  // the set that stored the slot's last rows
+        const bool head_due = (lq & 1) == 0 && Qi > 0;  // the previous pair's dense head
+        if (head_due && fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
+#pragma unroll 1
+        for (int j = set; j < U::OP; j += 2) {
+            const int gq = seq * U::OP + j, dp = gq & (U::NDP - 1);
+            mbar_wait_s(B.d_full + dp * 8, (gq / U::NDP) & 1);
+            tc5_fence_after();
+            float dd[32];
+            tmem_ld32(tm_lane + U::TM_D + dp * 32, dd);
+            tmem_wait_ld();
+            tc5_fence_before();
+            mbar_arrive_s(B.d_empty + dp * 8);
+            float v[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const float lo = fmaxf(dd[c], dd[16 + c]), hi = fmaxf(dd[c + 8], dd[24 + c]);
+                const float other = __shfl_xor_sync(0xffffffffu, odd ? lo : hi, 1);  // what the pair lane stores, it gets
+                v[c] = fmaxf(fmaxf(odd ? hi : lo, other), 0.f);                       // the bias is in already; relu(max(.)) == max relu(.)
             }
-            if (rp >= 4) {  // output pair rp-4 has been complete since the issuer's step rp-2: a whole step of slack
-                const int j = rp - 4, gq = seq * U::OP + j, dp = gq & (U::NDP - 1);
-                mbar_wait_s(B.d_full + dp * 8, (gq / U::NDP) & 1);
-                tc5_fence_after();
-                float dd[32];
-                tmem_ld32(tm_lane + U::TM_D + dp * 32, dd);
-                tmem_wait_ld();
-                tc5_fence_before();
-                mbar_arrive_s(B.d_empty + dp * 8);
-                float v[8];
+            if (live) {
+                uint4 pk;
+                pk.x = Ops<T>::pack(v[0], v[1]); pk.y = Ops<T>::pack(v[2], v[3]);
+                pk.z = Ops<T>::pack(v[4], v[5]); pk.w = Ops<T>::pack(v[6], v[7]);
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(p2 + j * N::PW2 * 256), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w) : "memory");
+                if (dump) {
+                    float* dg = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + (lq & 1) * kG * N::P2_STRIDE + o2 + j * N::PW2 * N::C2;
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const float lo = fmaxf(dd[c], dd[16 + c]), hi = fmaxf(dd[c + 8], dd[24 + c]);
-                    const float other = __shfl_xor_sync(0xffffffffu, odd ? lo : hi, 1);  // what the pair lane stores, it gets
-                    v[c] = fmaxf(fmaxf(odd ? hi : lo, other), 0.f);                       // the bias is in already; relu(max(.)) == max relu(.)
+                    for (int c = 0; c < 8; c++) dg[c] = v[c];
                 }
-                if (live) {
-                    uint4 pk;
-                    pk.x = Ops<T>::pack(v[0], v[1]); pk.y = Ops<T>::pack(v[2], v[3]);
-                    pk.z = Ops<T>::pack(v[4], v[5]); pk.w = Ops<T>::pack(v[6], v[7]);
-                    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(p2 + j * N::PW2 * 256), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w) : "memory");
-                    if (dump) {
-                        float* dg = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + (lq & 1) * kG * N::P2_STRIDE + o2 + j * N::PW2 * N::C2;
-#pragma unroll
-                        for (int c = 0; c < 8; c++) dg[c] = v[c];
-                    }
-                }
-            }
-            if ((lq & 1) == 0 && Qi > 0) {  // the previous pair's dense head
-                if (rp == U::FC1_STEP) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
-                if (rp == U::FC2_STEP) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi - 1);
             }
         }
+        if (head_due && fc2_mine) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi - 1);
         fence_proxy_async();  // p2 was written by ordinary stores and is read by the tensor core
         mbar_arrive_s(B.p2_full + buf2 * 8);
         seq++;
