@@ -61,8 +61,16 @@ void InferenceBolt::emit_front_nulls_locked() {
 }
 
 void InferenceBolt::completion_main() {
-    std::vector<sib_result> res(256);
+    // One native pass formats a whole poll's messages into the arena (sib_poll_json_batch); they are then emitted and
+    // acked under ONE hold of the collector's monitor instead of one lock, one buffer and one formatting call per tuple.
+    // (sib.shared = 1 keeps the per-tuple path: results of a shared engine are copied per client, sib_client_poll.)
+    constexpr int kMax = 256;
+    std::vector<sib_result> res(kMax);
     std::vector<char> buf(1 << 14);
+    std::vector<char> arena((size_t)kMax * 256);
+    std::vector<uint64_t> tags(kMax);
+    std::vector<uint32_t> offs(kMax + 1);
+    std::vector<int32_t> status(kMax);
     std::unique_lock<std::mutex> lk(mu_);
     for (;;) {
         emit_front_nulls_locked();
@@ -73,11 +81,32 @@ void InferenceBolt::completion_main() {
             continue;
         }
         lk.unlock();
-        int n = shared_ ? sib_client_poll(client_, res.data(), (int)res.size(), 2000) : sib_poll(engine_, res.data(), (int)res.size(), 2000);
+        int n;
+        if (shared_) n = sib_client_poll(client_, res.data(), kMax, 2000);
+        else n = sib_poll_json_batch(engine_, arena.data(), arena.size(), tags.data(), offs.data(), status.data(), kMax, 2000);
         lk.lock();
-        for (int i = 0; i < n; i++) {
+        if (n > 0 && !shared_) {
+            std::lock_guard<std::mutex> sync(collector_->monitor);  // synchronized (collector) { for (...) { emit; ack; } }
+            for (int i = 0; i < n; i++) {
+                while (!fifo_.empty() && fifo_.front().null_msg) {  // decode failures keep their place in the order
+                    collector_->emit(Values{});
+                    collector_->ack(fifo_.front().tuple);
+                    fifo_.pop_front();
+                }
+                if (fifo_.empty()) break;  // cannot happen: every submitted tuple has a FIFO entry
+                Values v;
+                if (status[i] == SIB_OK && offs[i + 1] > offs[i]) {
+                    v.is_null = false;
+                    v.message.assign(arena.data() + offs[i], offs[i + 1] - offs[i]);
+                }
+                collector_->emit(v);
+                collector_->ack(fifo_.front().tuple);
+                fifo_.pop_front();
+            }
+        }
+        for (int i = 0; shared_ && i < n; i++) {
             emit_front_nulls_locked();
-            if (fifo_.empty()) break;  // cannot happen: every submitted tuple has a FIFO entry
+            if (fifo_.empty()) break;
             Pending p = fifo_.front();
             fifo_.pop_front();
             Values v;

@@ -71,7 +71,8 @@ struct Slot {
     // FILLING: accepting tuples. SEALED: closed to new tuples and queued for launch, but some submitter is still
     // copying its images in (writers > 0). INFLIGHT: copies and kernels issued. READY: results in h_probs.
     // HANDED: results given out by sib_poll, slot recycled at the next poll.
-    enum State { FREE, FILLING, SEALED, INFLIGHT, READY, HANDED };
+    // REDO: complete on the GPU, a poller is re-reading the tuples the decode kernel declined (engine lock released).
+    enum State { FREE, FILLING, SEALED, INFLIGHT, REDO, READY, HANDED };
     Atom<int> state{FREE};       // written under the engine lock; the last writer of a tuple reads it without (see written())
     float* h_in = nullptr;       // pinned, max_batch x img
     float* h_probs = nullptr;    // pinned, max_batch x ncls
@@ -133,7 +134,8 @@ struct sib_engine {
     void free_slot(Slot& s);
     int run_forward(const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax, GuardScratch* g,
                     cudaStream_t st);
-    void redo_flagged_locked(Slot& s);    // json_on_gpu: tuples the decode kernel declined go through the host decoder
+    void redo_flagged(Slot& s);           // json_on_gpu: tuples the decode kernel declined go through the host decoder (no lock held)
+    std::atomic<uint64_t> launches{0};    // kernels launched; bumped from the batch path and the synchronous paths alike
     int seal_locked(int si, int reason);  // stop filling; launches at once unless a writer is still copying
     int launch_locked(int si);
     void deadline_main();
@@ -153,6 +155,7 @@ int sib_engine::alloc_dev(DevBufs& d, bool with_io) {
         CU_TRY(cudaMalloc((void**)&d.guard.d_list, mb * sizeof(int32_t)));
         CU_TRY(cudaMalloc((void**)&d.guard.d_count, 2 * sizeof(int32_t)));
         CU_TRY(cudaMemset(d.guard.d_count, 0, 2 * sizeof(int32_t)));
+        d.guard.self_reset = true;  // one stream per scratch: the guard kernel clears the counter behind itself
     }
     return SIB_OK;
 }
@@ -209,14 +212,14 @@ int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_l
     int e;
     if (cfg.precision == SIB_PREC_FP32) {
         e = launch_forward_fp32(dm, d_in, n, nullptr, nullptr, d_probs, d_logits, d_argmax, nullptr, st);
-        stats.kernel_launches += 1;
+        launches.fetch_add(1, std::memory_order_relaxed);
     } else {
         const bool guard = cfg.guard != 0;
         e = launch_forward_tc(tc, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, nullptr, st);
-        stats.kernel_launches += 1;
+        launches.fetch_add(1, std::memory_order_relaxed);
         if (!e && guard) {
-            e = launch_guard_fp32(model.preset, dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, st);
-            stats.kernel_launches += 1;
+            e = launch_guard_fp32(model.preset, dm, d_in, n, *g, d_probs, d_logits, d_argmax, st);
+            launches.fetch_add(1, std::memory_order_relaxed);
         }
     }
     if (e) {
@@ -262,7 +265,7 @@ int sib_engine::launch_locked(int si) {
         in_bytes += s.text_used + (size_t)s.n_text * 16;
         if (rc == SIB_OK) {
             int ke = launch_json_decode(s.d_text, s.d_tdesc, s.n_text, s.dev.d_in, s.d_tflags, (int)model.in_h, (int)model.in_w, (int)model.in_c, s.stream);
-            stats.kernel_launches += 1;
+            launches.fetch_add(1, std::memory_order_relaxed);
             if (ke) { set_error(std::string("json decode kernel: ") + cudaGetErrorString((cudaError_t)ke)); rc = SIB_ECUDA; }
         }
         chk(cudaMemcpyAsync(s.h_tflags, s.d_tflags, (size_t)s.n_text * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream), "D2H text flags");
@@ -272,7 +275,7 @@ int sib_engine::launch_locked(int si) {
     const size_t n_img = (size_t)s.images;
     int32_t* d_arg = reinterpret_cast<int32_t*>(s.dev.d_probs + n_img * nc);
     GuardScratch g = s.dev.guard;
-    g.d_count = d_arg + n_img;
+    g.d_out_count = d_arg + n_img;  // the guard kernel leaves the list length here and clears its own counter
     const bool guarded = cfg.precision != SIB_PREC_FP32 && cfg.guard;
     if (rc == SIB_OK) rc = run_forward(s.dev.d_in, s.images, s.dev.d_probs, nullptr, d_arg, &g, s.stream);
     const size_t d2h = (n_img * (nc + 1) + (guarded ? 1 : 0)) * sizeof(float);
@@ -298,14 +301,20 @@ int sib_engine::launch_locked(int si) {
 extern "C" int sib_forward_sync(sib_engine* e, const float* x, int n, float* probs, float* logits, int32_t* argmax);
 
 // The decode kernel only takes one-instance tuples in canonical form; whatever it flagged is read again here with
-// the host decoder, which owns the complete Jackson semantics (leniencies, N > 1, error classes). Rare path.
-void sib_engine::redo_flagged_locked(Slot& s) {
-    const size_t nc = model.n_classes;
-    std::vector<float> tmp;
+// the host decoder, which owns the complete Jackson semantics (leniencies, N > 1, error classes). Rare path, but a
+// producer that writes 17-digit doubles sends every tuple down it: the slot is parked in state REDO and the engine
+// lock is NOT held here, so submitters and the deadline thread go on, and all flagged tuples of the slot share one
+// forward pass instead of a synchronous round trip each.
+void sib_engine::redo_flagged(Slot& s) {
+    const size_t nc = model.n_classes, img = model.img_elems;
+    std::vector<float> tmp, all;
+    struct Todo { Entry* en; int n; size_t at; };
+    std::vector<Todo> todo;
+    uint64_t gpu_ok = 0, redone = 0;
     for (auto& en : s.entries) {
         if (en.text < 0) continue;
-        if (!s.h_tflags[en.text]) { stats.json_gpu_decoded++; continue; }
-        stats.json_host_redone++;
+        if (!s.h_tflags[en.text]) { gpu_ok++; continue; }
+        redone++;
         const char* txt = s.h_text + s.h_tdesc[4 * en.text];
         const size_t len = (size_t)s.h_tdesc[4 * en.text + 1];
         const long cap = (long)(len / 2 + 8);
@@ -316,16 +325,27 @@ void sib_engine::redo_flagged_locked(Slot& s) {
         if (nf < 0 || dims[1] != model.in_h || dims[2] != model.in_w || dims[3] != model.in_c || dims[0] > cfg.max_batch) {
             en.n = 0; en.status = SIB_ESHAPE; continue;
         }
+        todo.push_back(Todo{&en, (int)dims[0], all.size()});
+        all.insert(all.end(), tmp.begin(), tmp.begin() + (size_t)dims[0] * img);
+    }
+    int total = 0;
+    for (auto& t : todo) total += t.n;
+    std::vector<float> probs((size_t)total * nc);
+    std::vector<int32_t> arg((size_t)total);
+    const bool ok = total == 0 || sib_forward_sync(this, all.data(), total, probs.data(), nullptr, arg.data()) == SIB_OK;
+    for (auto& t : todo) {
+        if (!ok) { t.en->n = 0; t.en->status = SIB_ECUDA; continue; }
+        const size_t first = t.at / img;
         SideResult sr;
-        sr.probs.resize((size_t)dims[0] * nc);
-        sr.argmax.resize((size_t)dims[0]);
-        if (sib_forward_sync(this, tmp.data(), (int)dims[0], sr.probs.data(), nullptr, sr.argmax.data()) != SIB_OK) {
-            en.n = 0; en.status = SIB_ECUDA; continue;
-        }
-        en.n = (int)dims[0];
-        en.side = (int)s.side.size();
+        sr.probs.assign(probs.begin() + first * nc, probs.begin() + (first + (size_t)t.n) * nc);
+        sr.argmax.assign(arg.begin() + first, arg.begin() + first + (size_t)t.n);
+        t.en->n = t.n;
+        t.en->side = (int)s.side.size();
         s.side.push_back(std::move(sr));
     }
+    std::lock_guard<std::mutex> lk(mu);
+    stats.json_gpu_decoded += gpu_ok;
+    stats.json_host_redone += redone;
 }
 
 void sib_engine::deadline_main() {
@@ -595,7 +615,9 @@ extern "C" int sib_submit_json(sib_engine* e, uint64_t tag, const char* utf8, si
         std::unique_lock<std::mutex> lk(e->mu);
         raw = !e->fifo.empty() || (e->filling >= 0 && e->slots[e->filling].images > 0);
     }
-    if (raw && len >= 16 && len <= json_gpu_max_text()) {
+    // (a tuple longer than a whole slot's text area -- small max_batch, long number text -- goes to the host decoder:
+    // after the area of a non-empty slot is closed below, a fresh, empty one always has room for it)
+    if (raw && len >= 16 && len <= json_gpu_max_text() && len + 32 <= e->slots[0].text_cap) {
         // Raw path: the text itself goes into the slot's pinned text area and is decoded by a kernel after the H2D.
         // The engine learns only at completion whether the tuple was well-formed (sib_result.status).
         Slot* s;
@@ -688,8 +710,12 @@ extern "C" int sib_flush(sib_engine* e) {
     return SIB_OK;
 }
 
-extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us) {
-    if (!e || !out || max <= 0) return SIB_EINVAL;
+// sib_poll and sib_poll_json_batch. `budget` (may be null): bytes of message text the caller can still take; a tuple whose
+// upper bound does not fit stays queued for the next poll (never the first tuple of a poll, so progress is guaranteed
+// for any arena that holds one message).
+static size_t message_bound(int n, int nc) { return 32 + (size_t)n * ((size_t)nc * 18 + 4); }  // json_encode's own bound
+
+static int poll_core(sib_engine* e, sib_result* out, int max, int timeout_us, size_t* budget) {
     std::unique_lock<std::mutex> lk(e->mu);
     // results handed out by the previous poll are dead now: recycle their slots
     for (auto& s : e->slots)
@@ -700,7 +726,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
     for (;;) {
         while (got < max && !e->fifo.empty()) {
             Slot& s = e->slots[e->fifo.front()];
-            if (s.state == Slot::SEALED) break;  // a submitter is still copying into it
+            if (s.state == Slot::SEALED || s.state == Slot::REDO) break;  // a submitter is still copying into it | another poller is re-reading it
             if (s.state == Slot::INFLIGHT) {
                 cudaError_t q = cudaEventQuery(s.done);
                 if (q == cudaErrorNotReady) break;
@@ -710,18 +736,31 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
                 }
                 s.state = Slot::READY;
                 if (e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard) e->stats.guard_recomputed += (uint64_t)s.r_guard_n[0];
-                if (s.n_text > 0) e->redo_flagged_locked(s);
+                if (s.n_text > 0) {  // host decoder for what the decode kernel declined: outside the engine lock
+                    s.state = Slot::REDO;
+                    lk.unlock();
+                    e->redo_flagged(s);
+                    lk.lock();
+                    s.state = Slot::READY;
+                    e->cv.notify_all();
+                }
             }
+            bool arena_full = false;
             while (got < max && s.next_entry < s.entries.size()) {
                 const Entry& en = s.entries[s.next_entry++];
                 if (en.n == 0 && en.status == SIB_OK) continue;  // reservation that was given back (see sib_submit_json)
+                if (budget) {
+                    const size_t need = message_bound(en.n, nc);
+                    if (need > *budget && got > 0) { s.next_entry--; arena_full = true; break; }
+                    *budget -= need < *budget ? need : *budget;
+                }
                 sib_result& r = out[got++];
                 r.tag = en.tag; r.n = en.n; r.n_classes = nc; r.status = s.status != SIB_OK ? s.status : en.status; r.reserved = 0;
                 if (en.n == 0) { r.probs = nullptr; r.argmax = nullptr; }
                 else if (en.side >= 0) { r.probs = s.side[(size_t)en.side].probs.data(); r.argmax = s.side[(size_t)en.side].argmax.data(); }
                 else { r.probs = s.h_probs + (size_t)en.offset * nc; r.argmax = s.r_argmax + en.offset; }
             }
-            if (s.next_entry == s.entries.size()) {
+            if (s.next_entry == s.entries.size() && !arena_full) {
                 s.state = Slot::HANDED;
                 e->fifo.pop_front();
             } else {
@@ -735,7 +774,7 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
         const bool pending = !e->fifo.empty() || (e->filling >= 0 && e->slots[e->filling].images > 0);
         if (!pending) break;
         if (timeout_us > 0 && Clock::now() >= t_end) break;
-        if (!e->fifo.empty() && e->slots[e->fifo.front()].state == Slot::SEALED) {
+        if (!e->fifo.empty() && (e->slots[e->fifo.front()].state == Slot::SEALED || e->slots[e->fifo.front()].state == Slot::REDO)) {
             if (timeout_us < 0) e->cv.wait(lk);
             else e->cv.wait_until(lk, t_end);
         } else if (!e->fifo.empty()) {
@@ -757,6 +796,35 @@ extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us)
     return got;
 }
 
+extern "C" int sib_poll(sib_engine* e, sib_result* out, int max, int timeout_us) {
+    if (!e || !out || max <= 0) return SIB_EINVAL;
+    return poll_core(e, out, max, timeout_us, nullptr);
+}
+
+// Batched egress: every message of a poll formatted in one native pass, outside the engine lock.
+extern "C" int sib_poll_json_batch(sib_engine* e, char* arena, size_t cap, uint64_t* tags, uint32_t* offsets, int32_t* status,
+                                   int max, int timeout_us) {
+    if (!e || !arena || !tags || !offsets || !status || max <= 0) return SIB_EINVAL;
+    if (cap < message_bound(1, (int)e->model.n_classes)) { set_error("sib_poll_json_batch: arena smaller than one message"); return SIB_ECAP; }
+    static thread_local std::vector<sib_result> res;
+    if ((int)res.size() < max) res.resize((size_t)max);
+    size_t budget = cap;
+    const int n = poll_core(e, res.data(), max, timeout_us, &budget);
+    size_t at = 0;
+    for (int i = 0; i < n; i++) {
+        tags[i] = res[i].tag;
+        status[i] = res[i].status;
+        offsets[i] = (uint32_t)at;
+        if (res[i].status == SIB_OK && res[i].probs) {
+            const long len = json_encode(res[i].probs, res[i].n, res[i].n_classes, arena + at, cap - at);
+            if (len > 0) at += (size_t)len;          // written without a terminating NUL: the offsets delimit it
+            else status[i] = (int32_t)(len < 0 ? len : SIB_ECAP);  // cannot happen: the bound was reserved above
+        }
+    }
+    if (n >= 0) offsets[n] = (uint32_t)at;
+    return n;
+}
+
 extern "C" long sib_format_json(const sib_result* r, char* buf, size_t cap) {
     if (!r || !buf || !r->probs) return SIB_EINVAL;
     return json_encode(r->probs, r->n, r->n_classes, buf, cap);
@@ -766,6 +834,7 @@ extern "C" int sib_stats_get(sib_engine* e, sib_stats* out) {
     if (!e || !out) return SIB_EINVAL;
     std::unique_lock<std::mutex> lk(e->mu);
     *out = e->stats;
+    out->kernel_launches = e->launches.load(std::memory_order_relaxed);
     return SIB_OK;
 }
 
@@ -780,12 +849,19 @@ extern "C" int sib_forward_sync(sib_engine* e, const float* x, int n, float* pro
         const int b = std::min(n - done, e->cfg.max_batch);
         std::memcpy(s.h_in, x + (size_t)done * img, (size_t)b * img * sizeof(float));
         CU_TRY(cudaMemcpyAsync(s.dev.d_in, s.h_in, (size_t)b * img * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-        int r = e->run_forward(s.dev.d_in, b, s.dev.d_probs, logits ? s.dev.d_logits : nullptr, s.dev.d_argmax, &s.dev.guard, s.stream);
+        const bool guarded = e->cfg.precision != SIB_PREC_FP32 && e->cfg.guard;
+        GuardScratch g = s.dev.guard;
+        int32_t* d_listed = reinterpret_cast<int32_t*>(s.dev.d_probs + (size_t)e->cfg.max_batch * (nc + 1));  // spare words behind the result block
+        g.d_out_count = d_listed;
+        int r = e->run_forward(s.dev.d_in, b, s.dev.d_probs, logits ? s.dev.d_logits : nullptr, s.dev.d_argmax, &g, s.stream);
         if (r) return r;
+        int32_t listed = 0;
+        if (guarded) CU_TRY(cudaMemcpyAsync(&listed, d_listed, sizeof listed, cudaMemcpyDeviceToHost, s.stream));
         CU_TRY(cudaMemcpyAsync(s.h_probs, s.dev.d_probs, (size_t)b * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
         CU_TRY(cudaMemcpyAsync(s.h_argmax, s.dev.d_argmax, (size_t)b * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         if (logits) CU_TRY(cudaMemcpyAsync(logits + (size_t)done * nc, s.dev.d_logits, (size_t)b * nc * sizeof(float), cudaMemcpyDeviceToHost, s.stream));
         CU_TRY(cudaStreamSynchronize(s.stream));
+        if (guarded) { std::lock_guard<std::mutex> sl(e->mu); e->stats.guard_recomputed += (uint64_t)listed; }
         std::memcpy(probs + (size_t)done * nc, s.h_probs, (size_t)b * nc * sizeof(float));
         if (argmax) std::memcpy(argmax + done, s.h_argmax, (size_t)b * sizeof(int32_t));
         done += b;

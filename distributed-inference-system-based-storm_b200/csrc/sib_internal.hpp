@@ -83,7 +83,11 @@ int fp32_smem_bytes(const DeviceModel& m);
 struct GuardScratch {
     float* d_margin = nullptr;
     int32_t* d_list = nullptr;
-    int32_t* d_count = nullptr;
+    int32_t* d_count = nullptr;      // [0] list length, [1] ticket of the guard kernel's CTAs (self_reset)
+    int32_t* d_out_count = nullptr;  // self_reset: where the guard kernel leaves the launch's list length (may be null)
+    // true: the guard kernel's last CTA clears the counter for the next launch (no cudaMemsetAsync between batches);
+    // false: launch_forward_tc clears it stream-ordered at the head of every call (callers that share the scratch)
+    bool self_reset = false;
 };
 struct TcWeights {
     void* d_packed = nullptr;  // weights pre-swizzled into mma fragment order (half or bf16) + fp32 biases
@@ -113,7 +117,7 @@ struct EngineView {
 bool engine_view(sib_engine* e, EngineView* out);
 
 // fp32 recompute of the listed images, one image per CTA (sib_kernels_guard.cu). LeNet-5 presets only.
-int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const int32_t* d_list,
-                      const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, void* stream);
+int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const GuardScratch& g, float* d_probs,
+                      float* d_logits, int32_t* d_argmax, void* stream);
 
 }  // namespace sib

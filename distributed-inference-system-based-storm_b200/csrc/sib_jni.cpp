@@ -41,13 +41,39 @@ JNIEXPORT void JNICALL Java_dke_model_NativeInfer_close(JNIEnv*, jclass, jlong h
 }
 
 JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_submitJson(JNIEnv* env, jclass, jlong hh, jlong tag, jbyteArray utf8) {
+    // The submit takes the engine's mutex and may answer SIB_EAGAIN after waiting on it: none of that is allowed inside
+    // a Get/ReleasePrimitiveArrayCritical region (no blocking, no other JNI calls), so the text is copied out first
+    // (10-40 KB, one memcpy; the decoder then writes the floats straight into the pinned slot).
     JHandle* h = (JHandle*)(intptr_t)hh;
-    jsize n = env->GetArrayLength(utf8);
-    jbyte* p = (jbyte*)env->GetPrimitiveArrayCritical(utf8, nullptr);   // no copy: decoded straight into the pinned slot
-    jint rc = h->c ? sib_client_submit_json(h->c, (uint64_t)tag, (const char*)p, (size_t)n)
-                   : sib_submit_json(h->e, (uint64_t)tag, (const char*)p, (size_t)n);
-    env->ReleasePrimitiveArrayCritical(utf8, p, JNI_ABORT);
-    return rc;
+    const jsize n = env->GetArrayLength(utf8);
+    static thread_local std::vector<jbyte> text;
+    if ((jsize)text.size() < n) text.resize((size_t)n);
+    env->GetByteArrayRegion(utf8, 0, n, text.data());
+    return h->c ? sib_client_submit_json(h->c, (uint64_t)tag, (const char*)text.data(), (size_t)n)
+                : sib_submit_json(h->e, (uint64_t)tag, (const char*)text.data(), (size_t)n);
+}
+
+// Batched egress: one crossing per poll. `arena` is a direct ByteBuffer the bolt keeps; the messages land in it back to
+// back, tags/offsets/status describe them (sib_poll_json_batch). Own engines only (h->e).
+JNIEXPORT jint JNICALL Java_dke_model_NativeInfer_pollJsonBatch(JNIEnv* env, jclass, jlong hh, jobject arena, jlongArray tags,
+                                                                 jintArray offsets, jintArray status, jint timeout_us) {
+    JHandle* h = (JHandle*)(intptr_t)hh;
+    if (!h || !h->e) return SIB_EINVAL;
+    char* base = (char*)env->GetDirectBufferAddress(arena);
+    const jlong cap = env->GetDirectBufferCapacity(arena);
+    const int max = env->GetArrayLength(tags);
+    if (!base || cap <= 0 || env->GetArrayLength(offsets) < max + 1 || env->GetArrayLength(status) < max) return SIB_EINVAL;
+    static thread_local std::vector<uint64_t> t;
+    static thread_local std::vector<uint32_t> o;
+    static thread_local std::vector<int32_t> st;
+    t.resize((size_t)max); o.resize((size_t)max + 1); st.resize((size_t)max);
+    const int n = sib_poll_json_batch(h->e, base, (size_t)cap, t.data(), o.data(), st.data(), max, timeout_us);
+    if (n > 0) {
+        env->SetLongArrayRegion(tags, 0, n, (const jlong*)t.data());
+        env->SetIntArrayRegion(offsets, 0, n + 1, (const jint*)o.data());
+        env->SetIntArrayRegion(status, 0, n, (const jint*)st.data());
+    }
+    return n;
 }
 
 JNIEXPORT void JNICALL Java_dke_model_NativeInfer_flush(JNIEnv*, jclass, jlong hh) {

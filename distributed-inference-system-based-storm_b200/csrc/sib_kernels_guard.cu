@@ -54,17 +54,31 @@ struct GNet {
 template <typename G>
 __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const float* __restrict__ in,
                                                            const int32_t* __restrict__ list,
-                                                           const int32_t* __restrict__ count, int cap,
+                                                           int32_t* count, int32_t* out_count, int self_reset, int cap,
                                                            float* __restrict__ probs, float* __restrict__ logits,
                                                            int32_t* __restrict__ argmax) {
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x;
-    const int n = min(*count, cap);
+    const int n = min(*reinterpret_cast<volatile int32_t*>(count), cap);
+    // self_reset: every CTA has read the length above before it takes a ticket; the last one to finish hands the
+    // length to the host's result block and clears counter and ticket for the next launch on this scratch
+    auto finish = [&]() {
+        if (!self_reset) return;
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            if (atomicAdd(count + 1, 1) == (int)gridDim.x - 1) {
+                if (out_count) *out_count = n;
+                count[0] = 0;
+                count[1] = 0;
+            }
+        }
+    };
     // The list is dealt out in contiguous, near-equal shares (they differ by at most one image), so every CTA is done
     // after the same number of passes; dealing whole 4-image passes round-robin left a second, mostly empty wave.
     const int per = n / (int)gridDim.x, rem = n % (int)gridDim.x;
     const int first = (int)blockIdx.x * per + min((int)blockIdx.x, rem), last = first + per + ((int)blockIdx.x < rem ? 1 : 0);
-    if (first >= last) return;
+    if (first >= last) { finish(); return; }
     const float* W = m.weights;
     const DeviceLayer L0 = m.layer[0], L1 = m.layer[1], L2 = m.layer[2], L3 = m.layer[3], L4 = m.layer[4];
     auto load_images = [&](int it, int imgs) {  // asynchronous copies: nothing waits until cp_async_wait_all()
@@ -269,11 +283,12 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             if (lane == 0 && argmax) argmax[img] = am;
         }
     }
+    finish();
 }
 
 template <typename G>
-int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected, const int32_t* d_list,
-                 const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, cudaStream_t st) {
+int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected, const GuardScratch& g, float* d_probs,
+                 float* d_logits, int32_t* d_argmax, cudaStream_t st) {
     static SmemLimit limit;                   // function attributes are per device
     static std::atomic<int> ctas_per_sm[64];  // per device; zero = not asked yet (threads may race, to the same value)
     int dev = 0, sms = 148;
@@ -291,20 +306,20 @@ int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected,
     }
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = max(1, min(expected, sms * ctas_per_sm[dev & 63].load()));  // one wave; a CTA's share may take several passes
-    guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, d_list, d_count, cap, d_probs, d_logits, d_argmax);
+    guard_fp32_kernel<G><<<grid, kGT, smem, st>>>(m, d_in, g.d_list, g.d_count, g.d_out_count, g.self_reset ? 1 : 0, cap, d_probs, d_logits, d_argmax);
     return (int)cudaGetLastError();
 }
 
 }  // namespace
 
 // Re-runs the images d_list[0 .. *d_count) in fp32 and overwrites their rows. preset: 0 mnist-lenet5, 1 cifar-lenet5.
-int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const int32_t* d_list,
-                      const int32_t* d_count, float* d_probs, float* d_logits, int32_t* d_argmax, void* stream) {
+int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const GuardScratch& g, float* d_probs,
+                      float* d_logits, int32_t* d_argmax, void* stream) {
     if (n <= 0) return 0;
     const int expected = min(n, max(256, n / 16));  // grid sizing only; the kernel grid-strides over the real count
     if (preset == 0)
-        return launch_guard<GNet<28, 28, 1>>(m, d_in, n, expected, d_list, d_count, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
-    return launch_guard<GNet<32, 32, 3>>(m, d_in, n, expected, d_list, d_count, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
+        return launch_guard<GNet<28, 28, 1>>(m, d_in, n, expected, g, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
+    return launch_guard<GNet<32, 32, 3>>(m, d_in, n, expected, g, d_probs, d_logits, d_argmax, (cudaStream_t)stream);
 }
 
 }  // namespace sib

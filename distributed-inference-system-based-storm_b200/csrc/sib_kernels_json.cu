@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
     }
     // ---- pass B: record where every token starts (thread-sequential over its chunk, but cheap) ...
     unsigned short* pos = reinterpret_cast<unsigned short*>(s + ((len + 15) & ~15));  // elems x 2 bytes behind the text
+    unsigned short* endp = pos + kMaxElems;                                           // ... and where every token ends
     {
         int k = s_cnt[tid];
         for (int i = lo; i < hi; i++)
@@ -169,7 +170,14 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
         const double pw = c_pow10[ae > 22 ? 22 : ae];
         d = e10 < 0 ? d / pw : d * pw;
         if (k < elems) dst[k] = (float)(neg ? -d : d);
-        // -- punctuation between the previous token and this one
+        endp[k] = (unsigned short)p;
+    }
+    __syncthreads();
+    // ---- pass D: the punctuation between the previous token's END and this token must be exactly what the canonical
+    // nesting puts there. (Walking back only as far as "some digit" let a stray run that holds no token start but
+    // ends in a digit -- "7,e5,8", "7,.5,8", "7,+5,8" -- pass; the host decoder and Jackson reject those.)
+    for (int k = tid; k < elems; k += kJT) {
+        const int i = pos[k], p = endp[k];
         int q = i - 1;
         if (k == 0) {
             bool ok = back_expect(s, q, '[') && back_expect(s, q, '[') && back_expect(s, q, '[') && back_expect(s, q, '[') &&
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(kJT) json_decode_kernel(const unsigned char* _
             else if (w_i != 0) ok = back_expect(s, q, '[') && back_expect(s, q, ',') && back_expect(s, q, ']');
             else ok = back_expect(s, q, '[') && back_expect(s, q, '[') && back_expect(s, q, ',') && back_expect(s, q, ']') && back_expect(s, q, ']');
             while (ok && q >= 0 && is_ws(s[q])) q--;
-            ok = ok && q >= 0 && is_digit(s[q]);  // a number ends in a digit
+            ok = ok && q + 1 == (int)endp[k - 1];  // ... and nothing else since the previous number ended
             bad |= !ok;
         }
         if (k == elems - 1) {  // closing: ]]]] }  (bytes after the root object are ignored, like Jackson)
@@ -216,7 +224,7 @@ int launch_json_decode(const char* d_text, const int32_t* d_desc, int n_tuples, 
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    constexpr int smem = kMaxText + 16 + 2 * kMaxElems;
+    constexpr int smem = kMaxText + 16 + 4 * kMaxElems;
     const unsigned char* text = reinterpret_cast<const unsigned char*>(d_text);
     if (n_tuples <= sms) {  // fewer tuples than SMs: latency matters, every tuple has an SM to itself anyway
         static SmemLimit limit;

@@ -29,6 +29,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstring>
 #include <type_traits>
 #include <vector>
@@ -808,7 +809,10 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
                         if (P.argmax) P.argmax[img] = am;
                         const float mg = mx - second;
                         if (P.margin) P.margin[img] = mg;
-                        if (P.list && mg < P.tau) P.list[atomicAdd(P.count, 1)] = img;  // guard: recompute in fp32
+                        if (P.list && (!(mg >= P.tau * fmaxf(1.f, fabsf(mx) * (1.f / 12.f))) || !(fabsf(mx) <= 3.0e38f))) {  // guard: recompute in fp32 (threshold grows with the logits; a NaN margin is listed too)
+                            const int pos = atomicAdd(P.count, 1);
+                            if (pos < P.n) P.list[pos] = img;
+                        }
                     }
                 }
             }
@@ -1106,6 +1110,9 @@ int tc_prepare(const ModelDesc& m, int precision, TcWeights* out) {
     if (!tc_supported(m)) { set_error("tensor-core path covers the LeNet-5 presets only"); return SIB_EINVAL; }
     std::vector<uint32_t> w;
     const bool bf = precision == SIB_PREC_BF16;
+    if (!bf)  // half precision tops out at 65504: a larger weight would become Inf and every image NaN
+        for (float x : m.weights)
+            if (!(std::fabs(x) < 65504.f)) { set_error("a weight exceeds the half-precision range: open the engine with SIB_PREC_BF16 or SIB_PREC_FP32"); return SIB_EINVAL; }
     if (m.preset == 0) w = bf ? pack_weights<NetMnist, __nv_bfloat16>(m) : pack_weights<NetMnist, __half>(m);
     else w = bf ? pack_weights<NetCifar, __nv_bfloat16>(m) : pack_weights<NetCifar, __half>(m);
     out->bytes = w.size() * 4;
@@ -1139,8 +1146,10 @@ int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_pro
     p.tau = tau; p.dbg = d_dbg;
     if (guard) {
         p.margin = guard->d_margin; p.list = guard->d_list; p.count = guard->d_count;
-        cudaError_t e = cudaMemsetAsync(guard->d_count, 0, sizeof(int32_t), st);  // the list starts empty every launch
-        if (e != cudaSuccess) return (int)e;
+        if (!guard->self_reset) {  // shared scratch: the list starts empty because this call says so
+            cudaError_t e = cudaMemsetAsync(guard->d_count, 0, sizeof(int32_t), st);
+            if (e != cudaSuccess) return (int)e;
+        }  // else: the previous launch's guard kernel left the counter at zero
     }
     const bool bf = w.precision == SIB_PREC_BF16;
     if (w.preset == 0) return bf ? launch<NetMnist, __nv_bfloat16>(w, p, st) : launch<NetMnist, __half>(w, p, st);

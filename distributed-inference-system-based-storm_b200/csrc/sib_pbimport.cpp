@@ -286,9 +286,14 @@ int import_pb(const void* bytes, size_t n, std::vector<uint8_t>* blob, std::stri
     std::string why;
     const Node* cur = g.in(sm, 0);
     bool relu_seen = false;
+    // A GraphDef is not guaranteed acyclic (a hostile or corrupt file can feed a node its own output): every step of
+    // the walk below is counted, and no chain is longer than the node list.
+    size_t steps = 0;
+    const size_t max_steps = g.nodes.size() + 8;
     // ---- dense head
     for (;;) {
         if (!cur) return fail("dangling input while walking back from '" + sm->name + "'");
+        if (++steps > max_steps || dense.size() > (size_t)kMaxLayers) return fail("cycle in the graph at '" + cur->name + "'");
         if (cur->op == "Relu") { if (relu_seen) return fail("two Relu in a row at '" + cur->name + "'"); relu_seen = true; cur = g.in(cur, 0); continue; }
         if (cur->op == "Reshape" || cur->op == "Squeeze" || cur->op == "Flatten") {
             if (relu_seen) return fail("Relu directly after the flatten at '" + cur->name + "'");
@@ -324,10 +329,11 @@ int import_pb(const void* bytes, size_t n, std::vector<uint8_t>* blob, std::stri
     const Node* ph = nullptr;
     for (;;) {
         if (!cur) return fail("dangling input below the flatten");
+        if (++steps > max_steps || convs.size() > (size_t)kMaxLayers) return fail("cycle in the graph at '" + cur->name + "'");
         if (cur->op == "Placeholder") { ph = cur; break; }
         if (cur->op == "Reshape") { cur = g.in(cur, 0); continue; }
         bool relu = false, pool = false;
-        while (cur && (cur->op == "Relu" || cur->op == "MaxPool")) {
+        while (cur && (cur->op == "Relu" || cur->op == "MaxPool") && ++steps <= max_steps) {
             if (cur->op == "Relu") { if (relu) return fail("two Relu in one block at '" + cur->name + "'"); relu = true; }
             else {
                 if (pool) return fail("two MaxPool in one block at '" + cur->name + "'");

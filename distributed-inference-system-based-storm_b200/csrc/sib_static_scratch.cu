@@ -86,7 +86,7 @@ extern "C" int sib_forward_device_static(sib_engine* e, const float* d_nhwc, int
     g.d_list = reinterpret_cast<int32_t*>(base + kListOff);
     g.d_count = reinterpret_cast<int32_t*>(base + kCountOff);  // zeroed by launch_forward_tc at the head of the call
     int ce = sib::launch_forward_tc(*v.tc, d_nhwc, n, d_probs, d_logits, d_argmax, &g, v.tau, nullptr, stream);
-    if (!ce) ce = sib::launch_guard_fp32(v.preset, *v.dm, d_nhwc, n, g.d_list, g.d_count, d_probs, d_logits, d_argmax, stream);
+    if (!ce) ce = sib::launch_guard_fp32(v.preset, *v.dm, d_nhwc, n, g, d_probs, d_logits, d_argmax, stream);
     if (ce) {
         sib::set_error(std::string("sib_forward_device_static: ") + cudaGetErrorString((cudaError_t)ce));
         return SIB_ECUDA;

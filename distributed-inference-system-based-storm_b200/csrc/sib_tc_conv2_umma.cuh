@@ -76,6 +76,14 @@ template <typename T> __device__ __forceinline__ constexpr uint32_t umma_idesc_m
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
 }
 
+// max that hands a NaN on (fmaxf drops it): an overflowed half-precision activation turns into Inf - Inf = NaN one layer
+// later, and that NaN has to reach the logits so that the margin guard sends the image to the fp32 path
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+    float d;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+
 // barriers by shared-memory address
 __device__ __forceinline__ void mbar_arrive_s(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
@@ -222,9 +230,9 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
             float v[8];
 #pragma unroll
             for (int c = 0; c < 8; c++) {
-                const float lo = fmaxf(dd[c], dd[16 + c]), hi = fmaxf(dd[c + 8], dd[24 + c]);
+                const float lo = fmax_nan(dd[c], dd[16 + c]), hi = fmax_nan(dd[c + 8], dd[24 + c]);
                 const float other = __shfl_xor_sync(0xffffffffu, odd ? lo : hi, 1);  // what the pair lane stores, it gets
-                v[c] = fmaxf(fmaxf(odd ? hi : lo, other), 0.f);                       // the bias is in already; relu(max(.)) == max relu(.)
+                v[c] = fmax_nan(fmax_nan(odd ? hi : lo, other), 0.f);                 // the bias is in already; relu(max(.)) == max relu(.)
             }
             if (live) {
                 uint4 pk;

@@ -61,7 +61,7 @@ __device__ __forceinline__ void fcu_epilogue(const TcParams& P, unsigned char* s
     if (f < SBO / 16) {  // features past the padded K do not exist in the next layer's operand
 #pragma unroll
         for (int n = 0; n < 16; n++) {
-            const float x = f < REAL ? fmaxf(v[n] + b, 0.f) : 0.f;
+            const float x = f < REAL ? fmax_nan(v[n] + b, 0.f) : 0.f;
             sts16(dst + (n >> 3) * SBO + (n & 7) * 16, to_bits<T>(x));
             if (DBG && STAGE == 1 && P.dbg && blockIdx.x == 0 && Qi == 0 && f < 120)
                 P.dbg[2 * kG * N::PH1 * N::P1_ROW + N::DBG_P2 + n * 128 + f] = x;
@@ -141,6 +141,9 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
             for (int c = 0; c < 10; c++) lg[c] = scratch[lane * 10 + c];
             float mx = lg[0], second = -INFINITY;
             int am = 0;
+            bool finite = fabsf(lg[0]) <= 3.0e38f;
+#pragma unroll
+            for (int c = 1; c < 10; c++) finite = finite && fabsf(lg[c]) <= 3.0e38f;  // false for NaN and Inf
 #pragma unroll
             for (int c = 1; c < 10; c++) {
                 if (lg[c] > mx) { second = mx; mx = lg[c]; am = c; }
@@ -160,7 +163,13 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
             if (P.argmax) P.argmax[img] = am;
             const float mg = mx - second;
             if (P.margin) P.margin[img] = mg;
-            if (P.list && !(mg >= P.tau)) P.list[atomicAdd(P.count, 1)] = img;  // guard: recompute in fp32 (NaN margins too)
+            // guard: recompute in fp32. The half-precision error grows with the size of the logits, so the threshold does
+            // too (tau is calibrated for |logit| ~ 12); a NaN margin (overflowed activations) is listed as well.
+            // A logit that is not finite means an activation overflowed half precision: same treatment.
+            if (P.list && (!(mg >= P.tau * fmaxf(1.f, fabsf(mx) * (1.f / 12.f))) || !finite)) {
+                const int pos = atomicAdd(P.count, 1);
+                if (pos < P.n) P.list[pos] = img;  // a stale counter can never push the list past its capacity
+            }
         }
         __syncwarp();  // the scratch is rewritten by the next pair
     }

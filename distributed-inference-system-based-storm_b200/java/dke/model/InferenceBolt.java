@@ -26,6 +26,7 @@ public class InferenceBolt extends BaseRichBolt {
     private transient Thread completion;
     private transient volatile boolean stop;
     private transient long seq;
+    private transient boolean shared;   // sib.shared = 1: a view of the worker JVM's shared engine (per-tuple poll path)
     /** arrival order == emit order; a null-message entry is a tuple whose JSON did not parse */
     private transient ArrayDeque<Object[]> fifo;   // {Tuple, Boolean nullMsg}
 
@@ -50,9 +51,10 @@ public class InferenceBolt extends BaseRichBolt {
         int[] cfg = { conf(map, "sib.device", -1), ctx.getThisTaskIndex(), conf(map, "sib.max.batch", 0),
                       conf(map, "sib.deadline.us", 0), prec, conf(map, "sib.slots", 0), conf(map, "sib.guard", 1),
                       conf(map, "sib.json.gpu", 0), conf(map, "sib.strict.batching", 0), conf(map, "sib.shared", 0) };
+        shared = cfg[9] != 0;
         engine = NativeInfer.open(blob, cfg, 0f);
         if (engine == 0) throw new RuntimeException("InferenceBolt.prepare: " + NativeInfer.lastError());
-        completion = new Thread(this::completionLoop, "sib-completion");
+        completion = new Thread(shared ? this::completionLoopPerTuple : this::completionLoop, "sib-completion");
         completion.setDaemon(true);
         completion.start();
     }
@@ -79,7 +81,7 @@ public class InferenceBolt extends BaseRichBolt {
         }
     }
 
-    private void completionLoop() {
+    private void completionLoopPerTuple() {   // shared engine: results are copied per client, one String per JNI store
         long[] tags = new long[256];
         String[] msgs = new String[256];
         while (true) {
@@ -97,8 +99,48 @@ public class InferenceBolt extends BaseRichBolt {
                 for (int i = 0; i < n; i++) {
                     emitLeadingNulls();
                     Tuple t = (Tuple) fifo.pollFirst()[0];
-                    synchronized (collector) {          // OutputCollector is not thread-safe in Storm 1.x (KafkaBolt.java:133)
-                        collector.emit(new Values(msgs[i]));
+                    synchronized (collector) { collector.emit(new Values(msgs[i])); collector.ack(t); }
+                }
+            }
+        }
+    }
+
+    private void completionLoop() {
+        // Batched egress (sib_poll_json_batch): one JNI crossing and one native formatting pass per poll; the Strings are
+        // cut out of one direct buffer and handed to the collector under ONE monitor hold per batch (the per-tuple form
+        // paid a NewStringUTF, an array store and a synchronized block per tuple: at ~1 M tuples/s per GPU that monitor was
+        // the next ceiling). KafkaBolt downstream still gets one "message" String per tuple (KafkaBolt.java:123-124).
+        final int max = 256;
+        long[] tags = new long[max];
+        int[] offsets = new int[max + 1];
+        int[] status = new int[max];
+        java.nio.ByteBuffer arena = java.nio.ByteBuffer.allocateDirect(max * 256);
+        byte[] text = new byte[max * 256];
+        while (true) {
+            synchronized (fifo) {
+                emitLeadingNulls();
+                if (fifo.isEmpty()) {
+                    fifo.notifyAll();
+                    if (stop) return;
+                    try { fifo.wait(); } catch (InterruptedException e) { return; }
+                    continue;
+                }
+            }
+            int n = NativeInfer.pollJsonBatch(engine, arena, tags, offsets, status, 2000);
+            if (n <= 0) continue;
+            arena.position(0);
+            arena.get(text, 0, offsets[n]);
+            synchronized (fifo) {
+                synchronized (collector) {              // OutputCollector is not thread-safe in Storm 1.x (KafkaBolt.java:133)
+                    for (int i = 0; i < n; i++) {
+                        while (!fifo.isEmpty() && (Boolean) fifo.peekFirst()[1]) {   // decode failures keep their place
+                            collector.emit(new Values((String) null));
+                            collector.ack((Tuple) fifo.pollFirst()[0]);
+                        }
+                        Tuple t = (Tuple) fifo.pollFirst()[0];
+                        String msg = status[i] == 0 && offsets[i + 1] > offsets[i]
+                                ? new String(text, offsets[i], offsets[i + 1] - offsets[i], StandardCharsets.ISO_8859_1) : null;
+                        collector.emit(new Values(msg));
                         collector.ack(t);
                     }
                 }

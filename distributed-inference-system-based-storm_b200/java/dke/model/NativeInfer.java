@@ -20,5 +20,9 @@ public final class NativeInfer {
     public static native void flush(long engine);
     /** sib_poll + sib_format_json: fills tags[] and messages[] (null message = failed batch); returns count. */
     public static native int pollJson(long engine, long[] tags, String[] messages, int timeoutUs);
+    /** sib_poll_json_batch: one crossing per poll. The messages of up to tags.length tuples land back to back in the
+     *  direct buffer `arena`; message i is arena[offsets[i], offsets[i+1]) (offsets.length >= tags.length + 1), an empty
+     *  range with status[i] != 0 is a null message. Own engines only (not sib.shared). Returns the tuple count. */
+    public static native int pollJsonBatch(long engine, java.nio.ByteBuffer arena, long[] tags, int[] offsets, int[] status, int timeoutUs);
     public static native String lastError();
 }

@@ -65,6 +65,7 @@ SYMBOLS = {
     "sib_submit_f32": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
     "sib_submit_pinned": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_int]),
     "sib_poll": (C.c_int, [C.c_void_p, C.POINTER(Result), C.c_int, C.c_int]),
+    "sib_poll_json_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "sib_flush": (C.c_int, [C.c_void_p]),
     "sib_format_json": (C.c_long, [C.POINTER(Result), C.c_char_p, C.c_size_t]),
     "sib_stats_get": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
@@ -286,6 +287,18 @@ class Engine:
             am = np.ctypeslib.as_array(r.argmax, (r.n,)).copy()
             out.append((int(r.tag), pr, am, int(r.status)))
         return out
+
+    def poll_json_batch(self, max_results: int = 256, timeout_us: int = 0, arena_bytes: int = 1 << 16):
+        """sib_poll_json_batch -> list of (tag, message bytes | None, status): one native pass per poll."""
+        arena = np.empty(arena_bytes, np.uint8)
+        tags = np.empty(max_results, np.uint64)
+        offs = np.empty(max_results + 1, np.uint32)
+        st = np.empty(max_results, np.int32)
+        n = lib.sib_poll_json_batch(self._h, _p(arena), arena.size, _p(tags), _p(offs), _p(st), max_results, timeout_us)
+        if n < 0:
+            raise SibError(n, "sib_poll_json_batch")
+        raw = arena.tobytes()
+        return [(int(tags[i]), raw[offs[i]:offs[i + 1]] if st[i] == OK and offs[i + 1] > offs[i] else None, int(st[i])) for i in range(n)]
 
     def poll_json(self, max_results: int = 4096, timeout_us: int = 0):
         """-> list of (tag, message bytes) formatted by the library (PredObj JSON)."""

@@ -147,6 +147,17 @@ int sib_submit_pinned(sib_engine *e, uint64_t tag, const float *pinned_nhwc, int
  * pending. Returns the count. Invalidates pointers handed out by the previous poll. */
 int sib_poll(sib_engine *e, sib_result *out, int max, int timeout_us);
 
+/* Batched egress towards KafkaBolt (KafkaBolt.java:116-166 takes one "message" String per tuple):
+ * sib_poll + sib_format_json for up to max tuples in ONE native pass. The messages are written back to back into
+ * `arena` (no NUL between them); message i is arena[offsets[i] .. offsets[i+1]) and offsets must hold max+1 entries.
+ * status[i] != SIB_OK (SIB_EJSON, SIB_ESHAPE, ...) => empty range => the bolt emits a null message for that tuple
+ * (InferenceBolt.java:92-98). A tuple that no longer fits the arena stays queued for the next call; cap must hold at
+ * least one message (32 + rows * (18 * classes + 4) bytes). A binding turns the arena into Strings and emits them
+ * under one collector monitor per batch instead of one JNI crossing, one allocation and one lock per tuple.
+ * Returns the tuple count like sib_poll. */
+int sib_poll_json_batch(sib_engine *e, char *arena, size_t cap, uint64_t *tags, uint32_t *offsets, int32_t *status,
+                        int max, int timeout_us);
+
 /* Launch the partially filled batch now (bolt cleanup(), tests). */
 int sib_flush(sib_engine *e);
 
@@ -163,7 +174,10 @@ int sib_stats_get(sib_engine *e, sib_stats *out);
 int sib_forward_sync(sib_engine *e, const float *nhwc_host, int n, float *probs, float *logits, int32_t *argmax);
 
 /* Device-resident form (kernel-level timing): pointers are CUDA device pointers on the engine's device, stream is
- * a cudaStream_t (NULL = the CUDA default stream). Asynchronous: the work is only ordered on that stream. d_logits / d_argmax may be NULL. Needs n <= max_batch. */
+ * a cudaStream_t (NULL = the CUDA default stream). Asynchronous: the work is only ordered on that stream. d_logits / d_argmax may be NULL. Needs n <= max_batch.
+ * With the guard on, all calls on one engine share the guard's scratch (margins, low-margin list, counter): calls whose
+ * GPU work overlaps (different streams, no ordering between them) race on it -- order them, or give each stream its own
+ * engine. */
 int sib_forward_device(sib_engine *e, const float *d_nhwc, int n, float *d_probs, float *d_logits,
                        int32_t *d_argmax, void *stream);
 

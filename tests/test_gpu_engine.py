@@ -254,3 +254,39 @@ def test_co_located_bolts_share_one_engine(sib, oracle, presets):
         assert np.abs(np.concatenate([g[1] for g in got[ci]]) - pr[mine]).max() <= 1e-5
     for c in clients + [other]:
         c.close()
+
+
+def test_poll_json_batch_formats_a_whole_poll_like_the_per_tuple_path(sib, oracle, presets):
+    """sib_poll_json_batch (batched egress towards KafkaBolt, KafkaBolt.java:116-166): the messages of one poll, written
+    back to back by one native pass, are byte for byte what sib_poll + sib_format_json give tuple by tuple, and within
+    fp32 noise of the oracle's writeValueAsString; order, a multi-row tuple and a small arena (tuples that do not fit stay
+    queued for the next call) included."""
+    import json
+    import time
+    m = presets["mnist-lenet5"]
+    ms = sib.modelspec
+    om = oracle.Model(m.to_blob())
+    x = ms.synthetic_images(m, 91, 40)
+    payloads = [ms.instances_json(x[i:i + 1]) for i in range(40)]
+    payloads[5] = ms.instances_json(x[5:8])          # three rows in one tuple
+
+    def run(batched):
+        with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=64, deadline_us=300, strict_batching=True) as e:
+            for i, p in enumerate(payloads):
+                assert e.submit_json(i, p) > 0
+            e.flush()
+            got, t0 = [], time.time()
+            while len(got) < 40 and time.time() - t0 < 20:
+                if batched:
+                    got += [(t, msg) for t, msg, st in e.poll_json_batch(max_results=7, timeout_us=100000, arena_bytes=1500)]
+                else:
+                    got += e.poll_json(timeout_us=100000)
+        return got
+
+    per_tuple, batch = run(False), run(True)
+    assert [g[0] for g in batch] == list(range(40))
+    assert batch == per_tuple
+    for i, (tag, msg) in enumerate(batch):
+        got = np.array(json.loads(msg)["predictions"], np.float32)
+        ref = np.array(json.loads(om.execute(payloads[i]))["predictions"], np.float32)
+        assert got.shape == ((3, 10) if i == 5 else (1, 10)) and np.abs(got - ref).max() <= 1e-5

@@ -161,3 +161,42 @@ def test_auto_decode_uses_both_decoders_and_gives_the_same_bits(sib, presets):
     assert [g[0] for g in got] == list(range(300))
     assert np.concatenate([g[1] for g in got]).tobytes() == want.tobytes()
     assert 0 < st.json_gpu_decoded < 300                  # some went each way
+
+
+def test_gpu_decode_rejects_strays_between_numbers(sib, presets):
+    """A run that holds no token start but ends in a digit ("7,e5,8", "7,.5,8", "7,+5,8", "7,E3,8", "7 e5]") and a
+    leading zero are malformed for Jackson and for the host decoder; the device decoder must not let them through
+    either: every one of them comes back an error (the bolt emits a null message), never a prediction."""
+    m = presets["cifar-lenet5"]
+    ms = sib.modelspec
+    x = ms.synthetic_images(m, 85, 2)
+    good = ms.instances_json(x[:1])
+    assert good.startswith(b'{"instances":[[[[') and b"," in good
+    bad = [good.replace(b",", b"," + stray + b",", 1) for stray in (b"e5", b".5", b"+5", b"E3")]   # [a,e5,b,c]
+    bad.append(good.replace(b"]", b" e5]", 1))                                                       # [a,b,c e5]
+    bad.append(good.replace(b"[[[[", b"[[[[0", 1))                                                   # leading zero
+    assert all(t != good for t in bad)
+    tuples = [good] + bad + [ms.instances_json(x[1:2])]
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=16, deadline_us=10**6, json_on_gpu=True, strict_batching=True) as e:
+        got = _run(e, tuples)
+    assert got[0][3] == 0 and got[-1][3] == 0
+    for g in got[1:-1]:
+        assert g[3] == sib.native.EJSON and g[1] is None, g[3]
+
+
+def test_long_tuple_with_tiny_text_area_goes_to_the_host_decoder(sib, presets):
+    """max_batch = 1 gives a slot a text area smaller than one 17-digit MNIST tuple (~16 KB): the tuple must take the
+    host decoder instead of being copied past the end of the pinned text buffer."""
+    m = presets["mnist-lenet5"]
+    ms = sib.modelspec
+    x = ms.synthetic_images(m, 86, 3)
+    payloads = [json.dumps({"instances": x[i:i + 1].astype(np.float64).tolist()}).encode() for i in range(3)]  # 17 digits
+    assert min(len(p) for p in payloads) > 12000
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=1, deadline_us=200, json_on_gpu=True) as e:
+        got = _run(e, payloads)
+        st = e.stats()
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=8) as h:
+        ref, _, _ = h.forward_sync(x)
+    assert [g[3] for g in got] == [0, 0, 0]
+    assert np.concatenate([g[1] for g in got]).tobytes() == ref.tobytes()
+    assert st.json_gpu_decoded == 0

@@ -185,3 +185,63 @@ def test_engine_micro_batches_on_tc_path(sib, oracle, presets):
         P = np.concatenate([p for _, p, _, _ in got])
         assert np.abs(P - pr).max() <= 1e-2
         assert (np.concatenate([a for _, _, a, _ in got]) == pr.argmax(1)).all()
+
+
+def _scaled_model(sib, m, layer, factor):
+    import copy
+    mm = copy.deepcopy(m)
+    L = mm.layers[layer]
+    nw = L.a * L.b * L.c * L.d if L.kind == 1 else L.a * L.b
+    w = mm.weights.copy()
+    w[L.w_off:L.w_off + nw] *= np.float32(factor)
+    mm.weights = w
+    return mm
+
+
+def test_guard_holds_for_0_255_pixels_and_scaled_weights(sib, oracle, presets):
+    """The reference takes whatever float[][][][] the producer sends (InstObj.java:8), e.g. raw 0..255 pixels, and whatever
+    weights the SavedModel holds. Half-precision error grows with the size of the numbers, so the guard's threshold grows
+    with the logits: the guarded argmax must still equal the fp32 oracle's wherever the fp64 margin is not a tie."""
+    m = presets["cifar-lenet5"]
+    n = 4096
+    x255 = (sib.modelspec.synthetic_images(m, 68, n) * np.float32(255.0)).astype(np.float32)
+    cases = [(m, x255), (_scaled_model(sib, m, 4, 8.0), sib.modelspec.synthetic_images(m, 69, n))]
+    for model, x in cases:
+        om = oracle.Model(model.to_blob())
+        lg, pr = om.forward(x, threads=0)
+        with sib.native.Engine(model.to_blob(), precision=sib.native.PREC_FP16, max_batch=n, guard=True) as e:
+            gp, gl, ga = e.forward_sync(x)
+            st = e.stats()
+        assert np.isfinite(gl).all()
+        scale = np.abs(lg).max() / 12.9
+        assert np.abs(gl - lg).max() <= 5e-2 * max(1.0, scale)
+        bad = np.nonzero(ga != lg.argmax(1))[0]
+        if len(bad):
+            lg64, _ = om.forward64(x[bad])
+            s = np.sort(lg64, 1)
+            assert (s[:, -1] - s[:, -2] < 1e-5 * max(1.0, scale)).all(), (bad, s[:, -1] - s[:, -2])
+        assert 0 < st.guard_recomputed < n // 2           # the threshold scaled with the logits, it did not list everything
+
+
+def test_overflowing_activations_fall_to_the_fp32_guard(sib, oracle, presets):
+    """Weights that push conv1's outputs past 65504 make the half-precision path produce Inf/NaN; a NaN margin must be
+    listed for the fp32 recompute like a small one (`!(margin >= tau)`), so the caller still gets the fp32 network."""
+    m = _scaled_model(sib, presets["mnist-lenet5"], 0, 1.0e5)
+    x = sib.modelspec.synthetic_images(m, 70, 512)
+    lg, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=512, guard=True) as e:
+        gp, gl, ga = e.forward_sync(x)
+        st = e.stats()
+    assert np.isfinite(gp).all()
+    s = np.sort(lg.astype(np.float64), 1)
+    clear = s[:, -1] - s[:, -2] > 1e-3 * np.abs(lg).max()
+    assert (ga[clear] == lg.argmax(1)[clear]).all()
+    assert st.guard_recomputed >= int(clear.sum()) // 2   # (nearly) everything went through the guard
+
+
+def test_half_range_check_on_weights(sib, presets):
+    m = _scaled_model(sib, presets["mnist-lenet5"], 2, 1.0e7)
+    with pytest.raises(sib.native.SibError):
+        sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=16)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_BF16, max_batch=16) as e:
+        assert e is not None

@@ -123,6 +123,47 @@ def test_mutated_bytes_never_crash():
     assert outcomes["err"] > 0 and outcomes["ok"] + outcomes["err"] == 400
 
 
+def test_tf113_shaped_fixture_imports_to_the_preset_blob():
+    """tests/golden/lenet_tf113_saved_model.pb is assembled field by field from TF 1.13's public .proto files by
+    tests/golden/make_tf113_fixture.py -- a second encoder that shares nothing with pb_writer.py -- in the shape a real
+    frozen tf.layers LeNet export has: meta_info_def, saver_def, signature_def, Const -> Identity reads, the
+    Shape/StridedSlice/Pack/Reshape flatten, MatMul + Add, an unknown batch dimension, a control input."""
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    pb = open(os.path.join(here, "golden", "lenet_tf113_saved_model.pb"), "rb").read()
+    m = modelspec.make_preset("mnist-lenet5")
+    assert native.import_pb(pb) == m.to_blob()
+    info = native.describe(pb)
+    assert (info.in_h, info.in_w, info.in_c, info.n_classes) == (28, 28, 1, 10)
+    # the committed bytes are what the committed generator writes
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_tf113_fixture", os.path.join(here, "golden", "make_tf113_fixture.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    assert gen.build_saved_model(m) == pb
+
+
+def test_cyclic_graphs_are_refused_not_followed():
+    """A GraphDef can feed a node its own output; the walk must stop with an error, not loop or grow without bound."""
+    f = pw.attr_type(pw.DT_FLOAT)
+    w = np.zeros((4, 3), np.float32)
+    b = np.zeros(3, np.float32)
+    base = [pw.node("input", "Placeholder", dtype=f, shape=pw.attr_shape([-1, 4, 4, 1])),
+            pw.node("w", "Const", dtype=f, value=pw.attr_tensor(w)), pw.node("b", "Const", dtype=f, value=pw.attr_tensor(b))]
+    dense_cycle = base + [pw.node("mm", "MatMul", ["add", "w"]), pw.node("add", "Add", ["mm", "b"]),   # add -> mm -> add ...
+                          pw.node("output/Softmax", "Softmax", ["add"])]
+    reshape_cycle = base + [pw.node("fl", "Reshape", ["fl", "shape"]), pw.node("mm", "MatMul", ["fl", "w"]),
+                            pw.node("add", "Add", ["mm", "b"]), pw.node("output/Softmax", "Softmax", ["add"])]
+    relu_cycle = base + [pw.node("r", "Relu", ["p"]), pw.node("p", "MaxPool", ["r"], ksize=pw.attr_ints([1, 2, 2, 1]),
+                                                               strides=pw.attr_ints([1, 2, 2, 1]), padding=pw.attr_s("VALID")),
+                         pw.node("fl", "Reshape", ["r", "shape"]), pw.node("mm", "MatMul", ["fl", "w"]),
+                         pw.node("add", "Add", ["mm", "b"]), pw.node("output/Softmax", "Softmax", ["add"])]
+    for nodes in (dense_cycle, reshape_cycle, relu_cycle):
+        with pytest.raises(native.SibError) as e:
+            native.import_pb(pw.graph(nodes))
+        assert e.value.code == native.EINVAL
+
+
 @pytest.mark.gpu
 def test_engine_runs_from_saved_model_pb():
     """prepare() can hand the extracted saved_model.pb straight to sib_engine_open."""
