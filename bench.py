@@ -36,6 +36,20 @@ import numpy as np  # noqa: E402
 METRIC = "images/sec"
 
 
+def _modelspec():
+    """modelspec.py alone (numpy only), WITHOUT importing the package: the package's __init__ dlopens libsib.so, and the
+    reference arm must not have the product library in its process."""
+    import importlib.util
+    if "sib_modelspec_only" in sys.modules:
+        return sys.modules["sib_modelspec_only"]
+    path = os.path.join(ROOT, "distributed-inference-system-based-storm_b200", "modelspec.py")
+    spec = importlib.util.spec_from_file_location("sib_modelspec_only", path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["sib_modelspec_only"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -108,11 +122,10 @@ def cpu_per_tuple(model, seconds: float, threads: int = 0):
     """The reference's shape on the host cores: one forward per image (batch 1 per call, InferenceBolt.java:81-85),
     `threads` executors each owning a contiguous share. Bounded by wall time. -> (img/s, cores, sample text)."""
     import oracle
-    import sib_b200 as sib
     om = oracle.Model(model.to_blob())
     cores = oracle.max_threads() if threads <= 0 else threads
     chunk = 256 * cores
-    x = sib.modelspec.synthetic_images(model, 0, chunk)
+    x = _modelspec().synthetic_images(model, 0, chunk)
     om.forward(x[:cores], threads=cores)  # warm
     done, t0 = 0, time.perf_counter()
     while True:
@@ -129,9 +142,8 @@ def cpu_generous(model, seconds: float):
     try:
         import torch
         import torch_ref
-        import sib_b200 as sib
         torch.set_num_threads(os.cpu_count() or 8)
-        x = sib.modelspec.synthetic_images(model, 0, 256)
+        x = _modelspec().synthetic_images(model, 0, 256)
         blob = model.to_blob()
         torch_ref.forward(blob, x)
         done, t0 = 0, time.perf_counter()
@@ -141,6 +153,59 @@ def cpu_generous(model, seconds: float):
         return done / (time.perf_counter() - t0)
     except Exception as ex:  # noqa: BLE001
         return f"unavailable: {ex}"
+
+
+def cpu_t2_json(model, seconds: float):
+    """The bolt's real unit of work on the host cores: JSON tuple in -> JSON message out through the oracle's port of
+    execute() (InferenceBolt.java:69-100), one executor per core, one image per tuple. -> (tuples/s, cores, sample)."""
+    import oracle
+    ms = _modelspec()
+    om = oracle.Model(model.to_blob())
+    cores = oracle.max_threads()
+    x = ms.synthetic_images(model, 9, 32)
+    jp = [ms.instances_json(x[i:i + 1]) for i in range(32)]
+    batch = jp * max(1, (16 * cores) // 32)
+    om.run_tuples(batch[:cores], threads=cores)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        om.run_tuples(batch, threads=cores)
+        done += len(batch)
+        dt = time.perf_counter() - t0
+        if dt >= seconds:
+            break
+    return done / dt, cores, f"{done} one-image JSON tuples of {model.name} ({len(jp[0])} B each) in {dt:.1f} s"
+
+
+def tuple_rates(sib, model, blob, prec, guard, dev, rank, world, dist):
+    """What a Storm executor actually hands the bolt, flat out, at EVERY N (each rank drives its own GPU; whole-job rate =
+    tuples of all ranks / slowest rank's time): one-image fp32 tuples from pageable memory (a JVM heap float[]), and
+    one-image JSON tuples in -> JSON messages out with the host decoder and with the GPU decoder."""
+    from importlib import import_module
+    sharding = import_module("sib_b200.sharding")
+    native = sib.native
+    ms = sib.modelspec
+    cores = os.cpu_count() or 8
+    prod = max(1, min(6, cores // max(1, world) - 1))
+    x = ms.synthetic_images(model, 9 + rank, 32)
+    jp = [ms.instances_json(x[i:i + 1]) for i in range(32)]
+    fp = [x[i] for i in range(32)]
+    out = {"producers_per_gpu": prod, "json_bytes_per_tuple": int(np.mean([len(j) for j in jp])), "images_per_tuple": 1}
+
+    def one(key, payloads, mode, n, **kw):
+        with native.Engine(blob, device=dev, task_index=rank, max_batch=4096, deadline_us=200, precision=prec, n_slots=6, guard=guard, **kw) as e:
+            native.loadgen(e, payloads, 20000.0, 2000, mode=mode, producers=prod)
+            if dist is not None:
+                dist.barrier()
+            t0 = time.perf_counter()
+            r = native.loadgen(e, payloads, 5e7, n, mode=mode, producers=prod)
+            dt = time.perf_counter() - t0
+        u, t = sharding.aggregate(int(r["completed"]), dt, dist)
+        out[key] = u / t
+
+    one("t1_single_image_f32_tuples_per_s", fp, native.LG_F32, 400000)
+    one("t2_json_tuples_per_s_host_decode", jp, native.LG_JSON, 40000)
+    one("t2_json_tuples_per_s_gpu_decode", jp, native.LG_JSON, 200000, json_on_gpu=True)
+    return out
 
 
 def t2_and_latency(sib, model, blob, prec, guard):
@@ -194,8 +259,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import sib_b200 as sib
-    model = sib.modelspec.make_preset(args.preset)
+    model = _modelspec().make_preset(args.preset)  # numpy only: libsib.so is never loaded in this process
     per_step = max(1.0, min(8.0, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_per_tuple(model, 0.2)
@@ -211,7 +275,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, model, "fp32-cpu"),
+        "config": workload_config(args, model),
         "cpu_baseline": {"value": value, "unit": "images/s", "cores": cores, "kind": "port",
                          "sample": f"per step: {sample}; oracle/sib_oracle.c (TF-Java/Jackson cannot run: no JVM)"},
         "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -220,10 +284,10 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, model, precision: str) -> dict:
+def workload_config(args, model) -> dict:
     return {"workload": f"{model.name} ({model.h}x{model.w}x{model.c} -> softmax {model.n_classes}), "
                         f"{args.batch} images per step per GPU, SURVEY.md D2 synthetic pixels and weights",
-            "preset": model.name, "images_per_step_per_gpu": args.batch, "precision": precision,
+            "preset": model.name, "images_per_step_per_gpu": args.batch,
             "parallelism": f"executor-per-gpu x{args.gpus}, shuffle grouping, no collective",
             "l2": "4 rotating input buffers per GPU, each step's batch is read from HBM (4 x batch x image bytes > 126 MB L2)"}
 
@@ -300,6 +364,31 @@ def run_ours(args):
     step_ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(args.steps)]
     units, secs = sharding.aggregate(B * args.steps, t0_local, dist if world > 1 else None)
     value = units / secs
+    # ---- the same step, sustained: blocks of `steps` launches until >= 2 s have run, its own clock record. The 20-step
+    # region above is ~7 ms; this is what the kernel does once the chip is warm and power-managed.
+    sustained = None
+    if not os.environ.get("SIB_BENCH_NO_SUSTAINED"):
+        samp2 = ClockSampler(dev)
+        if rank == 0:
+            samp2.start()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        n_sus, t_w = 0, time.perf_counter()
+        while time.perf_counter() - t_w < 2.0:
+            for i in range(args.steps):
+                step(n_sus + i)
+            n_sus += args.steps
+            stream.synchronize()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        c2 = samp2.stop() if rank == 0 else None
+        u_s, t_s = sharding.aggregate(B * n_sus, e0.elapsed_time(e1) * 1e-3, dist if world > 1 else None)
+        sustained = {"value": u_s / t_s, "unit": "images/s", "steps": n_sus, "seconds": t_s, "clocks": c2}
     torch.cuda.current_stream().wait_stream(stream)
     checksum = float(d_probs.sum().item())  # every row sums to 1: B
     assert os.environ.get("SIB_BENCH_NOCHECK") or abs(checksum - B) < 1e-2 * B, checksum  # (diagnostic kernel builds skip the check)
@@ -374,6 +463,24 @@ def run_ours(args):
                 raise err[0]
             return got
 
+        # the link's own ceiling, measured now: pinned cudaMemcpyAsync H2D of the same batches, every rank at once
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            d_in[0].copy_(host_batches[0], non_blocking=True)
+            c0.record(stream)
+            reps = max(2, int(2e9 // (B * img * 4)))
+            for r_ in range(reps):
+                d_in[r_ % R].copy_(host_batches[r_ % R], non_blocking=True)
+            c1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ub, tb = sharding.aggregate(reps * B * img * 4, c0.elapsed_time(c1) * 1e-3, dist if world > 1 else None)
+        h2d_roof_gbs = ub / tb * 1e-9
+
         e2e_steps(max(1, min(args.warmup, 3)), 0)
         st0 = eng.stats()
         torch.cuda.synchronize()
@@ -392,10 +499,17 @@ def run_ours(args):
                "level": (f"T1: sib_submit_f32 (staged copy)" if args.e2e_copy else "T1: sib_submit_pinned (zero-copy, page-locked host fp32)")
                         + f" + sib_poll, {chunk} images per tuple, {n_thr} submitting threads per GPU",
                "h2d_bytes_per_step": (st1.h2d_bytes - st0.h2d_bytes) // n_e2e,
-               "d2h_bytes_per_step": (st1.d2h_bytes - st0.d2h_bytes) // n_e2e, "steps": n_e2e}
+               "d2h_bytes_per_step": (st1.d2h_bytes - st0.d2h_bytes) // n_e2e, "steps": n_e2e,
+               "images_per_tuple": chunk,
+               # T1's binding roof is the host->device link, not HBM: all ranks' pinned cudaMemcpyAsync at once, this run
+               "roof_gbs": h2d_roof_gbs, "roof": "pinned H2D copy of the same batches, all ranks concurrently, measured in this run",
+               "achieved_gbs": u2 / s2 * img * 4 * 1e-9, "frac": (u2 / s2 * img * 4 * 1e-9) / h2d_roof_gbs}
 
     guard_n = eng.stats().guard_recomputed
     eng.close()
+    tuples = None
+    if not args.skip_latency:
+        tuples = tuple_rates(sib, model, blob, prec, not args.no_guard, dev, rank, world, dist if world > 1 else None)
 
     if rank != 0:
         if world > 1:
@@ -412,11 +526,13 @@ def run_ours(args):
     step_med = statistics.median(step_ms)   # one step = forward kernel launch (+ the guard's recompute launch)
     k_ms = tc_ms if tc_ms is not None else step_med
     achieved = B * bpi / (k_ms * 1e-3) * 1e-9
-    traffic = None
+    traffic, traffic_src = None, None
     tr = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr):
+    if os.path.exists(tr):  # NOT measured by this run: dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture
         try:
-            traffic = json.load(open(tr)).get(f"{model.name}:{prec_name}:{B}")
+            tj = json.load(open(tr))
+            traffic = tj.get(f"{model.name}:{prec_name}:{B}")
+            traffic_src = tj.get("_source")
         except Exception:
             traffic = None
     line = {
@@ -424,16 +540,20 @@ def run_ours(args):
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": {"fp32": "f32", "fp16": "f16 operands, f32 accumulate",
                                        "bf16": "bf16 operands, f32 accumulate"}[prec_name],
-        "data": "synthetic", "config": workload_config(args, model, prec_name),
+        "data": "synthetic", "config": workload_config(args, model),
         "e2e": e2e, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+                     "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                     "step_frac": B * bpi / (step_med * 1e-3) * 1e-9 / hbm_peak,   # forward + guard kernels: what `value` is made of
                      "kernel": "forward_fp32_kernel" if prec_name == "fp32" else "forward_tc_kernel",
                      "kernel_ms": k_ms, "step_ms": step_med,
                      "guard_kernel_ms": (step_med - tc_ms) if tc_ms is not None else 0.0,
                      "algorithmic_bytes_per_image": bpi, "images_per_launch": B,
                      "flops_per_image": model.flops_per_image()},
         "clocks": clocks, "guard_recomputed_images": int(guard_n),
+        # (counted on the submit/poll path, i.e. over the e2e leg's images)
+        "guard_recomputed_fraction": (float(guard_n) / float(B * (e2e["steps"] + max(1, min(args.warmup, 3)))) if e2e else None),
+        "value_sustained": sustained, "tuples": tuples,
     }
     if not args.skip_cpu:
         v, cores, sample = cpu_per_tuple(model, args.cpu_seconds)
@@ -444,6 +564,9 @@ def run_ours(args):
         line["cpu_baseline"]["per_tuple_1_thread"] = v1
         line["cpu_baseline"]["per_tuple_4_threads"] = v4
         line["cpu_baseline"]["generous_torch_b256_all_cores"] = cpu_generous(model, 3.0)
+        vt, ct, st_ = cpu_t2_json(model, 5.0)   # the bolt's real unit of work: JSON tuple in -> JSON message out
+        line["cpu_baseline"]["t2_json_tuples_per_s_all_cores"] = vt
+        line["cpu_baseline"]["t2_sample"] = st_
     if not args.skip_latency and world == 1:
         line["t2_and_latency"] = t2_and_latency(sib, model, blob, prec, not args.no_guard)
     print(json.dumps(line), flush=True)
