@@ -111,13 +111,15 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
         for (int item = tid; item < imgs * G::PH1 * G::PW1; item += kGT) {
             const int g = item / (G::PH1 * G::PW1), pp = item % (G::PH1 * G::PW1);
             const int py = pp / G::PW1, px = pp % G::PW1;
-            float acc[2][2][G::C1];
+            // accumulators as channel pairs: packed fp32 FMA (fma.rn.f32x2) does two channels per issue slot; the stage
+            // was bound by issue slots (one LDS per 3-5 FFMA, profiles/ncu_guard_r01.txt), not by the FMA pipe
+            float2 acc[2][2][G::C1 / 2];
 #pragma unroll
             for (int a = 0; a < 2; a++)
 #pragma unroll
                 for (int b = 0; b < 2; b++)
 #pragma unroll
-                    for (int c = 0; c < G::C1; c++) acc[a][b][c] = 0.f;
+                    for (int c = 0; c < G::C1 / 2; c++) acc[a][b][c] = make_float2(0.f, 0.f);
             const float* ip = sm + G::S_IMG + g * G::IMG + ((2 * py) * G::W + 2 * px) * G::C;
 #pragma unroll 1
             for (int r = 0; r < 6; r++) {  // patch row r feeds output row dy with kernel row r-dy
@@ -132,20 +134,24 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
                     for (int kw = 0; kw < 5; kw++)
 #pragma unroll
                         for (int c = 0; c < G::C; c++) {
-                            const float* wp = sm + G::S_W1 + ((kh * 5 + kw) * G::C + c) * G::C1;  // broadcast reads
+                            const float2* wp = reinterpret_cast<const float2*>(sm + G::S_W1 + ((kh * 5 + kw) * G::C + c) * G::C1);  // broadcast reads
+                            const float x0 = row[kw * G::C + c], x1 = row[(kw + 1) * G::C + c];
+                            const float2 v0 = make_float2(x0, x0), v1 = make_float2(x1, x1);
 #pragma unroll
-                            for (int co = 0; co < G::C1; co++) {
-                                const float w = wp[co];
-                                acc[dy][0][co] = fmaf(row[kw * G::C + c], w, acc[dy][0][co]);
-                                acc[dy][1][co] = fmaf(row[(kw + 1) * G::C + c], w, acc[dy][1][co]);
+                            for (int co = 0; co < G::C1 / 2; co++) {
+                                const float2 w = wp[co];
+                                acc[dy][0][co] = __ffma2_rn(v0, w, acc[dy][0][co]);
+                                acc[dy][1][co] = __ffma2_rn(v1, w, acc[dy][1][co]);
                             }
                         }
                 }
             }
 #pragma unroll
-            for (int co = 0; co < G::C1; co++) {
-                const float mx = fmaxf(fmaxf(acc[0][0][co], acc[0][1][co]), fmaxf(acc[1][0][co], acc[1][1][co]));
-                sm[G::S_P1 + g * G::P1 + pp * G::C1 + co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + co], 0.f);
+            for (int co = 0; co < G::C1 / 2; co++) {
+                const float mx = fmaxf(fmaxf(acc[0][0][co].x, acc[0][1][co].x), fmaxf(acc[1][0][co].x, acc[1][1][co].x));
+                const float my = fmaxf(fmaxf(acc[0][0][co].y, acc[0][1][co].y), fmaxf(acc[1][0][co].y, acc[1][1][co].y));
+                sm[G::S_P1 + g * G::P1 + pp * G::C1 + 2 * co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + 2 * co], 0.f);
+                sm[G::S_P1 + g * G::P1 + pp * G::C1 + 2 * co + 1] = fmaxf(my + sm[G::S_W1 + G::NW1 + 2 * co + 1], 0.f);
             }
         }
         __syncthreads();
@@ -154,13 +160,13 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             const int q = item & 3, t2 = item >> 2;
             const int g = t2 / (G::PH2 * G::PW2), pos = t2 % (G::PH2 * G::PW2);
             const int py = pos / G::PW2, px = pos % G::PW2;
-            float acc[2][2][4];
+            float2 acc[2][2][2];
 #pragma unroll
             for (int a = 0; a < 2; a++)
 #pragma unroll
                 for (int b = 0; b < 2; b++)
 #pragma unroll
-                    for (int c = 0; c < 4; c++) acc[a][b][c] = 0.f;
+                    for (int c = 0; c < 2; c++) acc[a][b][c] = make_float2(0.f, 0.f);
             const float* ip = sm + G::S_P1 + g * G::P1 + ((2 * py) * G::PW1 + 2 * px) * G::C1;
 #pragma unroll 1
             for (int r = 0; r < 6; r++) {
@@ -176,17 +182,18 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 #pragma unroll
                         for (int c = 0; c < G::C1; c++) {
                             const float4 w = *reinterpret_cast<const float4*>(sm + G::S_W2 + ((kh * 5 + kw) * G::C1 + c) * G::C2 + 4 * q);
-                            const float v0 = row[kw * G::C1 + c], v1 = row[(kw + 1) * G::C1 + c];
-                            acc[dy][0][0] = fmaf(v0, w.x, acc[dy][0][0]); acc[dy][0][1] = fmaf(v0, w.y, acc[dy][0][1]);
-                            acc[dy][0][2] = fmaf(v0, w.z, acc[dy][0][2]); acc[dy][0][3] = fmaf(v0, w.w, acc[dy][0][3]);
-                            acc[dy][1][0] = fmaf(v1, w.x, acc[dy][1][0]); acc[dy][1][1] = fmaf(v1, w.y, acc[dy][1][1]);
-                            acc[dy][1][2] = fmaf(v1, w.z, acc[dy][1][2]); acc[dy][1][3] = fmaf(v1, w.w, acc[dy][1][3]);
+                            const float x0 = row[kw * G::C1 + c], x1 = row[(kw + 1) * G::C1 + c];
+                            const float2 v0 = make_float2(x0, x0), v1 = make_float2(x1, x1);
+                            const float2 wlo = make_float2(w.x, w.y), whi = make_float2(w.z, w.w);
+                            acc[dy][0][0] = __ffma2_rn(v0, wlo, acc[dy][0][0]); acc[dy][0][1] = __ffma2_rn(v0, whi, acc[dy][0][1]);
+                            acc[dy][1][0] = __ffma2_rn(v1, wlo, acc[dy][1][0]); acc[dy][1][1] = __ffma2_rn(v1, whi, acc[dy][1][1]);
                         }
                 }
             }
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                const float mx = fmaxf(fmaxf(acc[0][0][c], acc[0][1][c]), fmaxf(acc[1][0][c], acc[1][1][c]));
+                auto at = [&](int a, int b) { return (c & 1) ? acc[a][b][c >> 1].y : acc[a][b][c >> 1].x; };
+                const float mx = fmaxf(fmaxf(at(0, 0), at(0, 1)), fmaxf(at(1, 0), at(1, 1)));
                 sm[G::S_P2 + g * G::FEAT + pos * G::C2 + 4 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 4 * q + c], 0.f);  // (h,w,c) flatten
             }
         }
@@ -198,22 +205,24 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
             constexpr int KL = G::FEAT / G::KSL;
             const float4* wp = reinterpret_cast<const float4*>(W + L2.w_off) + (size_t)(ks * KL) * (G::F1 / 4) + n4;
             const float* xp = sm + G::S_P2 + ks * KL;
-            float4 a[kGI];
+            float2 alo[kGI], ahi[kGI];
 #pragma unroll
-            for (int g = 0; g < kGI; g++) a[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int g = 0; g < kGI; g++) alo[g] = ahi[g] = make_float2(0.f, 0.f);
 #pragma unroll 5
             for (int k = 0; k < KL; k++) {
                 const float4 w = __ldg(wp + (size_t)k * (G::F1 / 4));
+                const float2 wlo = make_float2(w.x, w.y), whi = make_float2(w.z, w.w);
 #pragma unroll
                 for (int g = 0; g < kGI; g++) {
                     const float x = xp[g * G::FEAT + k];
-                    a[g].x = fmaf(x, w.x, a[g].x); a[g].y = fmaf(x, w.y, a[g].y);
-                    a[g].z = fmaf(x, w.z, a[g].z); a[g].w = fmaf(x, w.w, a[g].w);
+                    const float2 xx = make_float2(x, x);
+                    alo[g] = __ffma2_rn(xx, wlo, alo[g]);
+                    ahi[g] = __ffma2_rn(xx, whi, ahi[g]);
                 }
             }
 #pragma unroll
             for (int g = 0; g < kGI; g++)
-                *reinterpret_cast<float4*>(sm + G::S_PART + (g * G::KSL + ks) * G::F1 + 4 * n4) = a[g];
+                *reinterpret_cast<float4*>(sm + G::S_PART + (g * G::KSL + ks) * G::F1 + 4 * n4) = make_float4(alo[g].x, alo[g].y, ahi[g].x, ahi[g].y);
         }
         __syncthreads();
         for (int o = tid; o < kGI * G::F1; o += kGT) {
