@@ -2,7 +2,11 @@
 
 Stated tolerances (DESIGN.md "precision"): the operands are rounded to 11 (fp16) or 8 (bf16) significant bits, the
 accumulation is fp32, logits of the D2 nets reach |x| ~ 12:
-    fp16: logits max-abs <= 5e-2, probabilities <= 1e-2        bf16: logits <= 0.30, probabilities <= 8e-2
+    fp16: logits max-abs <= 3e-2, probabilities <= 6e-3        bf16: logits <= 0.20, probabilities <= 5e-2
+(measured over 2^20 images per preset: fp16 2.1e-2, bf16 1.4e-1, profiles/batch_sweep_r01.jsonl and
+profiles/margin_error_r02.jsonl; tools/error_budget.py shows the ten rounding sources -- pixels, five weight tensors, four
+activation maps -- contributing ~1e-3 rms each, none dominant, so BASELINE.json's 1e-2 example for BF16 would take
+error compensation of every layer, i.e. three times the tensor work)
 argmax must equal the fp32 oracle's for every image (the margin guard recomputes near-ties in fp32 on the GPU),
 except where the fp64 shadow oracle shows a genuine tie (< 1e-5)."""
 import numpy as np
@@ -10,7 +14,7 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-TOL = {"fp16": (5e-2, 1e-2), "bf16": (0.30, 8e-2)}
+TOL = {"fp16": (3e-2, 6e-3), "bf16": (0.20, 5e-2)}
 
 
 def _prec(sib, name):
@@ -123,7 +127,7 @@ def test_tc_batch_edges(sib, oracle, presets, n):
     with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=4096) as e:
         gp, gl, ga = e.forward_sync(x)
     assert gp.shape == (n, 10)
-    assert np.abs(gl - lg).max() <= 5e-2 and np.abs(gp - pr).max() <= 1e-2
+    assert np.abs(gl - lg).max() <= 3e-2 and np.abs(gp - pr).max() <= 6e-3
 
 
 def test_tc_full_size_properties(sib, presets):
@@ -147,7 +151,7 @@ def test_tc_full_size_properties(sib, presets):
     with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP32, max_batch=n) as e:
         pf, lf, af = e.forward_sync(x)
     assert (a4 == af).all()                        # guarded tensor path == fp32 path, image by image
-    assert np.abs(l4 - lf).max() <= 5e-2
+    assert np.abs(l4 - lf).max() <= 3e-2
 
 
 def test_near_tie_policy(sib, oracle, presets):

@@ -23,7 +23,7 @@ def _run(e, entry, x, torch):
     return d_probs.cpu().numpy(), d_logits.cpu().numpy(), d_argmax.cpu().numpy()
 
 
-def test_static_scratch_entry_matches_engine_scratch_entry_twice_in_a_row(sib, presets):
+def test_static_scratch_entry_matches_engine_scratch_entry_twice_in_a_row(sib, oracle, presets):
     torch = pytest.importorskip("torch")
     m = presets["cifar-lenet5"]
     ms = sib.modelspec
@@ -45,6 +45,15 @@ def test_static_scratch_entry_matches_engine_scratch_entry_twice_in_a_row(sib, p
         with sib.native.Engine(m.to_blob(), device=0, precision=sib.native.PREC_FP32, max_batch=8192) as f:
             fp, fl, fa = f.forward_sync(batches[1])
         assert (got[1][2] == fa).all()
+        # ... and with the CPU oracle itself: argmax wherever the fp32 margin is not inside fp32 noise, logits within the
+        # half-precision path's stated tolerance (tests/test_gpu_tc.py)
+        om = oracle.Model(m.to_blob())
+        for (gp, gl, ga), x in zip(got, batches):
+            lg, pr = om.forward(x, threads=0)
+            so = np.sort(lg.astype(np.float64), 1)
+            clear = so[:, -1] - so[:, -2] > 1e-4
+            assert (ga[clear] == lg.argmax(1)[clear]).all()
+            assert np.abs(gl - lg).max() <= 3e-2 and np.abs(gp - pr).max() <= 6e-3
         # same result again on a third call (stale contents from call two)
         again = _run(e, e.forward_device_static, batches[0], torch)
         assert (again[2] == want[0][2]).all() and np.abs(again[1] - want[0][1]).max() <= 1e-6
