@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libsib.so")
 SOURCES = ["sib_model.cpp", "sib_pbimport.cpp", "sib_json.cpp", "sib_engine.cpp", "sib_shared.cpp", "sib_abi.cpp", "sib_bolt.cpp", "sib_jni.cpp", "sib_loadgen.cpp",
-           "sib_kernels_fp32.cu", "sib_kernels_tc.cu", "sib_kernels_guard.cu", "sib_static_scratch.cu", "sib_kernels_json.cu"]
+           "sib_kernels_fp32.cu", "sib_kernels_tc.cu", "sib_kernels_tcgen.cu", "sib_kernels_guard.cu", "sib_static_scratch.cu", "sib_kernels_json.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler",
          "-fPIC,-Wall,-Wno-unused-function", "-ccbin", "/usr/bin/g++"] + os.environ.get("SIB_NVCC_EXTRA", "").split()

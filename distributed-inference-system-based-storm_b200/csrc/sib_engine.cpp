@@ -217,9 +217,16 @@ int sib_engine::run_forward(const float* d_in, int n, float* d_probs, float* d_l
         const bool guard = cfg.guard != 0;
         e = launch_forward_tc(tc, d_in, n, d_probs, d_logits, d_argmax, guard ? g : nullptr, cfg.guard_tau, nullptr, st);
         launches.fetch_add(1, std::memory_order_relaxed);
-        if (!e && guard) {
+        if (!e && guard && !tc.generic) {
             e = launch_guard_fp32(model.preset, dm, d_in, n, *g, d_probs, d_logits, d_argmax, st);
             launches.fetch_add(1, std::memory_order_relaxed);
+        } else if (!e && guard) {
+            // any-shape models: the listed images go through the generic fp32 kernel; it does not know the counter
+            // protocol of guard_fp32_kernel, so the length is handed on and cleared by two small stream-ordered operations
+            e = launch_forward_fp32(dm, d_in, n, g->d_list, g->d_count, d_probs, d_logits, d_argmax, nullptr, st);
+            launches.fetch_add(1, std::memory_order_relaxed);
+            if (!e && g->d_out_count) e = (int)cudaMemcpyAsync(g->d_out_count, g->d_count, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+            if (!e) e = (int)cudaMemsetAsync(g->d_count, 0, sizeof(int32_t), st);
         }
     }
     if (e) {
@@ -430,7 +437,7 @@ extern "C" int sib_engine_open(const void* blob, size_t n, const sib_config* ucf
     if (c.device < 0) c.device = (c.task_index < 0 ? 0 : c.task_index) % ndev;  // executor -> GPU, MainTopology.java:62
     if (c.device >= ndev) { set_error("device ordinal out of range"); delete e; return SIB_EINVAL; }
     if (c.precision != SIB_PREC_FP32 && !tc_supported(e->model)) {
-        set_error("the tensor-core precisions cover the LeNet-5 presets (mnist-lenet5, cifar-lenet5); open this model with SIB_PREC_FP32");
+        set_error("this model's shapes do not fit the tensor-core kernels (conv output channels even and <= 64, dense input width even, <= 32 classes, 8 images of activations within shared memory); open it with SIB_PREC_FP32");
         delete e;
         return SIB_EINVAL;
     }
@@ -888,6 +895,7 @@ extern "C" int sib_forward_device(sib_engine* e, const float* d_nhwc, int n, flo
 extern "C" long sib_debug_stage_dump(sib_engine* e, const float* x, int n, float* out, long cap) {
     if (!e || !x || !out || n <= 0 || n > 16) return SIB_EINVAL;
     if (e->cfg.precision == SIB_PREC_FP32) { set_error("stage dump needs a tensor-core precision"); return SIB_EINVAL; }
+    if (e->tc.generic) { set_error("stage dump exists for the fused LeNet-5 kernel only"); return SIB_EINVAL; }
     const long need = (long)tc_debug_floats(e->model.preset);
     if (cap < need) return SIB_ECAP;
     std::unique_lock<std::mutex> lk(e->sync_mu);

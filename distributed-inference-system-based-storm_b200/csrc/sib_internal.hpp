@@ -89,12 +89,30 @@ struct GuardScratch {
     // false: launch_forward_tc clears it stream-ordered at the head of every call (callers that share the scratch)
     bool self_reset = false;
 };
+// Any-shape tensor-core kernel (sib_kernels_tcgen.cu): what the launch needs to know about the model.
+struct TcgLayer {
+    uint32_t kind, a, b, c, d, flags, w_off, b_off;  // as LayerDesc; w_off / b_off index the packed image (32-bit words)
+    int ks, nt;                                      // K steps of 16 (per kernel row for conv) and N tiles of 8
+};
+struct TcgPlan {
+    int in_h, in_w, in_c, n_layers, n_classes, img_elems;
+    int act_stride;  // halves per image and activation buffer (largest kept activation + slack)
+    int wsm_words;   // shared memory for the largest conv layer's fragments
+    int smem_bytes;
+    TcgLayer layer[kMaxLayers];
+};
 struct TcWeights {
     void* d_packed = nullptr;  // weights pre-swizzled into mma fragment order (half or bf16) + fp32 biases
     size_t bytes = 0;
     int preset = -1;
     int precision = SIB_PREC_FP16;
+    bool generic = false;      // true: the any-shape kernel (sib_kernels_tcgen.cu) with `plan`; false: the fused LeNet-5 kernel
+    TcgPlan plan{};
 };
+bool tcg_plan(const ModelDesc& m, TcgPlan* pl, std::string* why);
+std::vector<uint32_t> tcg_pack(const ModelDesc& m, int precision, TcgPlan* pl);
+int launch_forward_tcgen(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
+                         GuardScratch* guard, float tau, void* stream);
 bool tc_supported(const ModelDesc& m);
 int tc_prepare(const ModelDesc& m, int precision, TcWeights* out);  // uploads to the current device
 void tc_release(TcWeights* w);

@@ -325,6 +325,7 @@ int launch_guard(const DeviceModel& m, const float* d_in, int cap, int expected,
 int launch_guard_fp32(int preset, const DeviceModel& m, const float* d_in, int n, const GuardScratch& g, float* d_probs,
                       float* d_logits, int32_t* d_argmax, void* stream) {
     if (n <= 0) return 0;
+    if (preset != 0 && preset != 1) return (int)cudaErrorInvalidValue;  // other shapes: launch_forward_fp32 with the list
     const int expected = min(n, max(256, n / 16));  // grid sizing only; the kernel grid-strides over the real count
     if (preset == 0)
         return launch_guard<GNet<28, 28, 1>>(m, d_in, n, expected, g, d_probs, d_logits, d_argmax, (cudaStream_t)stream);

@@ -89,7 +89,9 @@ constexpr int kConv2Warps = SIB_CONV2_WARPS;
 #define SIB_REG_STAGE 1       // 0 forces the cp.async staging ring (kept for heights that are not a multiple of 2 batches)
 #endif
 #ifndef SIB_DYN_SPANS
-#define SIB_DYN_SPANS 0        // 1: conv1 warps claim their spans from a shared counter (measured: 219 vs 228 M img/s dealt round-robin)
+#define SIB_DYN_SPANS SIB_CONV2_UMMA  // 1: conv1 warps claim their spans from a shared counter. mma.sync build: 219 vs 228 M img/s dealt
+                                     // round-robin; tcgen05 build: 242 vs 238 (the sub-partitions carry unequal side loads: two conv2
+                                     // workers on three of them, the light issuer and head warps on the fourth)
 #endif
 #ifndef SIB_BIAS_IN_ACC1
 #define SIB_BIAS_IN_ACC1 0     // conv1 / conv2 accumulators start at the bias instead of adding it after the pool
@@ -134,7 +136,17 @@ struct Net {
     // distinct banks: stride/2 = 3*OW2 (mod 32) continues the 3-words-per-column progression across the seam
     static constexpr int P1_IMG = PH1 * P1_ROW + (((3 * OW2 - PH1 * P1_ROW / 2) % 32 + 32) % 32) * 2;
     static constexpr int P1_BUF = kG * P1_IMG + 16;                 // + slack for the K-padding over-read
-    static constexpr int NB1 = 3;                                   // p1 ring slots
+#ifndef SIB_NB1
+#define SIB_NB1 3
+#endif
+#ifndef SIB_NP2
+#define SIB_NP2 2
+#endif
+    // p1 ring slots / p2 buffers. -DSIB_NB1=4 -DSIB_NP2=1 fits (one p2 buffer is enough for the tcgen05 head, h2 overlays
+    // h1) and was measured: 238.0 M img/s against 238.0 with 3 / 2 -- the conv1 warps' wait for a p1 slot is imbalance
+    // among themselves (see SIB_DYN_SPANS), not ring depth.
+    static constexpr int NB1 = SIB_NB1;
+    static constexpr int NP2 = SIB_NP2;                             // p2 buffers (pairs)
     static constexpr int P2_STRIDE = FEAT + 8;                      // halves; +8 keeps A-fragment loads conflict-free
     // tcgen05 dense head: p2 / h1 / h2 are B operands (K-major, no swizzle: [img/8][k/8][img%8][k%8]), the weights A operands
     // ([m/8][k/8][m%8][k%8]); *_SBO = bytes between 8-row groups, 128 bytes between K chunks
@@ -172,10 +184,10 @@ struct Net {
     static constexpr int S_B2U = S_B1U;                                    // conv2 B operands for tcgen05 (5 KB); one variant at a time
     static constexpr int S_P1 = SIB_CONV2_UMMA ? S_B2U + 2 * B2U_KS_BYTES : SIB_CONV1_UMMA ? S_B1U + 2 * 5 * 512 : S_BIAS + 264 * 4;
     static constexpr int S_P2 = S_P1 + NB1 * P1_BUF * 2;
-    static constexpr int S_H1 = S_P2 + 2 * P2_BUF * 2;
+    static constexpr int S_H1 = S_P2 + NP2 * P2_BUF * 2;
     static constexpr int NHB = SIB_FC_IN_CONV2 ? 2 : 1;                    // h1/h2 buffers: dense heads of two pairs may overlap
-    static constexpr int S_H2 = S_H1 + (SIB_CONV2_UMMA ? 2 * F2_SBO : NHB * kPair * H1_STRIDE * 2);
-    static constexpr int S_FCS = S_H2 + (SIB_CONV2_UMMA ? 2 * F3_SBO : NHB * kPair * H2_STRIDE * 2);  // tcgen05 head: logits [16][10] fp32, lane <-> image transpose
+    static constexpr int S_H2 = SIB_CONV2_UMMA ? S_H1 : S_H1 + NHB * kPair * H1_STRIDE * 2;          // tcgen05 head: h2 overlays h1
+    static constexpr int S_FCS = SIB_CONV2_UMMA ? S_H1 + 2 * F2_SBO : S_H2 + NHB * kPair * H2_STRIDE * 2;  // tcgen05 head: logits [16][10] fp32, lane <-> image transpose
     static constexpr int S_RING = S_FCS + (SIB_CONV2_UMMA ? kPair * 10 * 4 : 0);
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
     static constexpr int URING_ROW = 2 * W * C + 16;                       // halves: Umma<N>::UROW
@@ -339,7 +351,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
     const uint32_t stage = smem_u32(smem + N::S_STAGE) + cw * N::PD * N::STAGE_ROW + chunk * 16;
     // SIB_DYN_SPANS: spans are claimed from a CTA-wide counter instead of being dealt round-robin, so the conv1 warps of a
     // sub-partition whose tensor pipe is less loaded (no conv2 warp there) end up taking more of them
-    uint32_t* span_ctr = reinterpret_cast<uint32_t*>(smem + N::S_TMEM);
+    uint32_t* span_ctr = reinterpret_cast<uint32_t*>(smem + N::S_TMEM + 4);  // (the first word holds the TMEM base address)
     auto claim = [&]() -> int {
         int v = 0;
         if (lane == 0) v = (int)atomicAdd(span_ctr, 1u);
@@ -873,9 +885,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
 #endif
         if (threadIdx.x == 0) {
             uint64_t* bars = reinterpret_cast<uint64_t*>(smem + N::S_BAR);
-#if !SIB_CONV1_UMMA && !SIB_CONV2_UMMA
-            *reinterpret_cast<uint32_t*>(smem + N::S_TMEM) = 0u;  // mma.sync build: the conv1 span counter lives here
-#endif
+            *reinterpret_cast<uint32_t*>(smem + N::S_TMEM + 4) = 0u;  // the conv1 span counter (SIB_DYN_SPANS)
 #if SIB_CONV2_UMMA
             {
                 using U = U2<N>;
@@ -943,7 +953,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
     // 20 warps = 5 warpgroups: conv1 x 12 | workers set 0 (q 0..2), conv2 issuer | workers set 1 (q 0..2), dense head (q 3).
     // A worker's / the head's TMEM lane quadrant is its hardware warp id mod 4. The launch gives every thread 96
     // registers; the last two warpgroups hand theirs down to 64 and the conv1 warpgroups take 128 (setmaxnreg).
-    static_assert(kConv1Warps == 12 && kConv2Warps == 6 && kIssueWarps == 1 && kFcWarps == 1 && !SIB_TAIL_FIRST && !SIB_FC_IN_CONV2 && !SIB_DYN_SPANS,
+    static_assert(kConv1Warps == 12 && kConv2Warps == 6 && kIssueWarps == 1 && kFcWarps == 1 && !SIB_TAIL_FIRST && !SIB_FC_IN_CONV2,
                   "tcgen05 conv2: warp layout");
     if (warp < kConv1Warps) {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 128;");
@@ -1104,12 +1114,37 @@ using NetCifar = Net<32, 32, 3>;
 
 }  // namespace
 
-bool tc_supported(const ModelDesc& m) { return m.preset == 0 || m.preset == 1; }
+// The two LeNet-5 presets take the fused persistent kernel of this file, every other model of the family the any-shape
+// kernel (sib_kernels_tcgen.cu), if its activations fit shared memory.
+static bool fused_shape(const ModelDesc& m) { return m.preset == 0 || m.preset == 1; }
+
+bool tc_supported(const ModelDesc& m) {
+    if (fused_shape(m)) return true;
+    TcgPlan pl;
+    return tcg_plan(m, &pl, nullptr);
+}
 
 int tc_prepare(const ModelDesc& m, int precision, TcWeights* out) {
-    if (!tc_supported(m)) { set_error("tensor-core path covers the LeNet-5 presets only"); return SIB_EINVAL; }
     std::vector<uint32_t> w;
     const bool bf = precision == SIB_PREC_BF16;
+    if (!fused_shape(m)) {
+        std::string why;
+        if (!tcg_plan(m, &out->plan, &why)) { set_error("tensor-core path: " + why + "; open this model with SIB_PREC_FP32"); return SIB_EINVAL; }
+        if (!bf)
+            for (float x : m.weights)
+                if (!(std::fabs(x) < 65504.f)) { set_error("a weight exceeds the half-precision range: open the engine with SIB_PREC_BF16 or SIB_PREC_FP32"); return SIB_EINVAL; }
+        w = tcg_pack(m, precision, &out->plan);
+        out->generic = true;
+        out->bytes = w.size() * 4;
+        out->preset = m.preset;
+        out->precision = precision;
+        if (cudaMalloc(&out->d_packed, out->bytes) != cudaSuccess ||
+            cudaMemcpy(out->d_packed, w.data(), out->bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+            set_error("tensor-core weight upload failed");
+            return SIB_ECUDA;
+        }
+        return SIB_OK;
+    }
     if (!bf)  // half precision tops out at 65504: a larger weight would become Inf and every image NaN
         for (float x : m.weights)
             if (!(std::fabs(x) < 65504.f)) { set_error("a weight exceeds the half-precision range: open the engine with SIB_PREC_BF16 or SIB_PREC_FP32"); return SIB_EINVAL; }
@@ -1139,6 +1174,7 @@ size_t tc_debug_floats(int preset) {
 int launch_forward_tc(const TcWeights& w, const float* d_in, int n, float* d_probs, float* d_logits, int32_t* d_argmax,
                       GuardScratch* guard, float tau, float* d_dbg, void* stream) {
     if (n <= 0) return 0;
+    if (w.generic) return launch_forward_tcgen(w, d_in, n, d_probs, d_logits, d_argmax, guard, tau, stream);
     cudaStream_t st = (cudaStream_t)stream;
     TcParams p{};
     p.wpack = static_cast<const uint32_t*>(w.d_packed);

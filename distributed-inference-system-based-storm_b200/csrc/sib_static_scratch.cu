@@ -76,6 +76,10 @@ extern "C" int sib_forward_device_static(sib_engine* e, const float* d_nhwc, int
                        "the fp32 path uses no scratch, call sib_forward_device");
         return SIB_EINVAL;
     }
+    if (v.preset != 0 && v.preset != 1) {
+        sib::set_error("sib_forward_device_static serves the LeNet-5 presets' fused kernel; this model runs on the any-shape kernel, call sib_forward_device");
+        return SIB_EINVAL;
+    }
     if (n == 0) return SIB_OK;
     if (cudaSetDevice(v.device) != cudaSuccess) { sib::set_error("cudaSetDevice failed"); return SIB_ECUDA; }
     unsigned char* base = nullptr;

@@ -181,9 +181,8 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         if (work < 0) break;
         const int Qi = lq >> 1;
         const int buf1 = lq % N::NB1, use1 = lq / N::NB1;
-        const int buf2 = Qi & 1, use2 = Qi >> 1;
+        const int buf2 = Qi % N::NP2, use2 = Qi / N::NP2;
         mbar_wait_s(B.p1_full + buf1 * 8, use1 & 1);
-        if ((lq & 1) == 0) mbar_wait_s(B.p2_empty + buf2 * 8, (use2 & 1) ^ 1);
         if (work == 0) {  // nothing to compute, keep the slot protocol going
             if (set == 0) mbar_arrive_s(B.p1_empty + buf1 * 8);
             mbar_arrive_s(B.p2_full + buf2 * 8);
@@ -217,6 +216,9 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         if (((U::RP - 1) & 1) == set) mbar_arrive_s(B.p1_empty + buf1 * 8);  // the set that stored the slot's last rows
         const bool head_due = (lq & 1) == 0 && Qi > 0;  // the previous pair's dense head
         if (head_due && fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
+        // first write into this pair's p2 buffer: fc1 of the pair that used it before must have read it (its mma ran
+        // under the row stores above)
+        if ((lq & 1) == 0) mbar_wait_s(B.p2_empty + buf2 * 8, (use2 & 1) ^ 1);
 #pragma unroll 1
         for (int j = set; j < U::OP; j += 2) {
             const int gq = seq * U::OP + j, dp = gq & (U::NDP - 1);

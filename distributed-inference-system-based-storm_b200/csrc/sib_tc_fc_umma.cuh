@@ -89,7 +89,7 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
     for (int Qi = 0;; Qi++) {
         const int pair = blockIdx.x + Qi * gridDim.x;
         if (pair >= nPairs) break;
-        const int buf = Qi & 1, use = Qi >> 1;
+        const int buf = Qi % N::NP2, use = Qi / N::NP2;
         const uint32_t ph = Qi & 1;
         // ---- fc1
         mbar_wait_s(B.p2_full + buf * 8, use & 1);

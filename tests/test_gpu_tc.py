@@ -54,7 +54,7 @@ def test_stage_dump_matches_oracle_stages(sib, oracle, presets, name):
     assert np.abs(got_h1 - h1).max() <= 8e-3 * max(1.0, np.abs(h1).max()), "fc1 stage"
 
 
-@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5", "mnist-wide", "cifar-wide"])
 @pytest.mark.parametrize("prec", ["fp16", "bf16"])
 @pytest.mark.parametrize("kind", ["uniform", "patches"])
 def test_tc_path_matches_oracle(sib, oracle, presets, name, prec, kind):
@@ -249,3 +249,40 @@ def test_half_range_check_on_weights(sib, presets):
         sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=16)
     with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_BF16, max_batch=16) as e:
         assert e is not None
+
+
+@pytest.mark.parametrize("name", ["mnist-wide", "cifar-wide"])
+def test_any_shape_kernel_guarded_argmax_is_the_fp32_argmax(sib, oracle, presets, name):
+    """The wide presets run on the any-shape tensor-core kernel (csrc/sib_kernels_tcgen.cu) with the same
+    margin guard as the fused kernel: listed images are re-run by the generic fp32 kernel, so the argmax is the fp32 one."""
+    m = presets[name]
+    n = 3000   # ragged last pass (8 images per CTA pass)
+    x = sib.modelspec.synthetic_images(m, 73, n)
+    om = oracle.Model(m.to_blob())
+    lg, pr = om.forward(x, threads=0)
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=2048, guard=True) as e:   # 3000 > 2048
+        gp, gl, ga = e.forward_sync(x)
+        st = e.stats()
+    assert np.abs(gl - lg).max() <= 3e-2 * max(1.0, np.abs(lg).max() / 12.9)
+    np.testing.assert_allclose(gp.sum(1), 1.0, atol=1e-5)
+    bad = np.nonzero(ga != lg.argmax(1))[0]
+    if len(bad):
+        lg64, _ = om.forward64(x[bad])
+        s = np.sort(lg64, 1)
+        assert (s[:, -1] - s[:, -2] < 1e-5).all(), (bad, s[:, -1] - s[:, -2])
+    assert 0 < st.guard_recomputed < n // 2
+
+
+def test_any_shape_kernel_on_an_odd_model(sib, oracle):
+    """A model nobody planned for: 22x20x2 input, conv blocks of 4 and 10 channels (a partial N tile), a 5x4 conv2 map (an
+    odd row count: floor pooling; ragged column tiles), dense 40 -> 36 -> 7: the tensor-core path must still match the oracle."""
+    m = sib.modelspec.custom_model("odd", 22, 20, 2, convs=[4, 10], dense=[36, 7], seed=11)
+    n = 77
+    x = sib.modelspec.synthetic_images(m, 74, n)
+    lg, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    for prec, tl in ((sib.native.PREC_FP16, 3e-2), (sib.native.PREC_BF16, 0.2)):
+        with sib.native.Engine(m.to_blob(), precision=prec, max_batch=64, guard=False) as e:
+            gp, gl, ga = e.forward_sync(x)
+        assert gp.shape == (n, 7)
+        assert np.abs(gl - lg).max() <= tl * max(1.0, np.abs(lg).max() / 12.9), float(np.abs(gl - lg).max())
+        assert (ga == gl.argmax(1)).all()
