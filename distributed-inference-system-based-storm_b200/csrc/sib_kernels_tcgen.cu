@@ -28,7 +28,7 @@ namespace sib {
 namespace {
 
 constexpr int kGI = 8;        // images per CTA pass
-constexpr int kGT = 256;      // threads
+constexpr int kGT = 512;      // threads (16 warps: 256 ran the wide presets 1.6x slower)
 constexpr int kSlack = 32;    // halves behind every image's activation: K padding may read past a row's end (x zero weights)
 
 template <typename T> struct GOps;
