@@ -24,7 +24,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // 6-10 per SM: that is 1 250-1 850 conv1 work items, 2-3 rounds of 768 threads. (256-thread CTAs, two per SM, with
 // 3-5 images each needed 3-4 conv1 rounds and 2 conv2 rounds for the same images: r01 guard profiles.)
 #ifndef SIB_GUARD_THREADS
-#define SIB_GUARD_THREADS 768
+#define SIB_GUARD_THREADS 512   // 16 warps x 128 registers: the 2x4 / 2x2x8 register tiles below need ~100 (768 threads cap at 85)
 #endif
 #ifndef SIB_GUARD_IMGS
 #define SIB_GUARD_IMGS 10
@@ -40,9 +40,9 @@ struct GNet {
     static constexpr int IMG = H * W * C, P1 = PH1 * PW1 * C1, FEAT = PH2 * PW2 * C2;
     static constexpr int NW1 = 25 * C * C1, NW2 = 25 * C1 * C2;
     // dense stages: as many k slices as the threads allow, so that the per-thread chain of L2 weight loads is short
-    static constexpr int KSL = kGT >= 600 ? FEAT / (FEAT % 20 == 0 ? 20 : 16) : 8;  // k slices of fc1 (x 30 float4 columns)
+    static constexpr int KSL = kGT >= 600 ? FEAT / (FEAT % 20 == 0 ? 20 : 16) : kGT >= 480 ? 16 : 8;  // k slices of fc1 (x 30 float4 columns)
     static constexpr int S2 = kGT >= 8 * F2 ? 8 : 3, K2 = F1 / S2;                   // k slices of fc2 (x 84 outputs)
-    static_assert(FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && S2 * F2 <= kGT && kGI * 32 <= kGT && F2 % 3 == 0 && F1 % S2 == 0, "mapping");
+    static_assert(PW1 % 2 == 0 && FEAT % KSL == 0 && IMG % 4 == 0 && KSL * (F1 / 4) <= kGT && S2 * F2 <= kGT && kGI * 32 <= kGT && F2 % 3 == 0 && F1 % S2 == 0, "mapping");
     // shared memory (floats). The images are dead once conv1 has run: the dense stages' scratch overlays them.
     static constexpr int DENSE = kGI * KSL * F1 + kGI * F1 + kGI * S2 * F2;
     static constexpr int S_IMG = 0, S_PART = 0, S_H1 = S_PART + kGI * KSL * F1, S_H2 = S_H1 + kGI * F1,
@@ -107,25 +107,26 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
         }
         cp_async_wait_all();
         __syncthreads();
-        // ---- conv1 + bias + ReLU + pool: item = (image, pooled position); 2x2 positions x 6 channels in registers
-        for (int item = tid; item < imgs * G::PH1 * G::PW1; item += kGT) {
-            const int g = item / (G::PH1 * G::PW1), pp = item % (G::PH1 * G::PW1);
-            const int py = pp / G::PW1, px = pp % G::PW1;
-            // accumulators as channel pairs: packed fp32 FMA (fma.rn.f32x2) does two channels per issue slot; the stage
-            // was bound by issue slots (one LDS per 3-5 FFMA, profiles/ncu_guard_r01.txt), not by the FMA pipe
-            float2 acc[2][2][G::C1 / 2];
+        // ---- conv1 + bias + ReLU + pool: item = (image, pooled row, PAIR of pooled columns): 2 x 4 conv outputs x 6 channels in
+        // registers as channel pairs (packed fp32 FMA, fma.rn.f32x2). The stage is bound by the broadcast weight loads from
+        // shared memory (stall_mio on them, short_scoreboard on the FMA behind them: profiles/ncu_guard_r02.txt); a 2x4 tile
+        // does twice the FMA per weight load of the 2x2 tile it replaces.
+        for (int item = tid; item < imgs * G::PH1 * (G::PW1 / 2); item += kGT) {
+            const int g = item / (G::PH1 * (G::PW1 / 2)), pp = item % (G::PH1 * (G::PW1 / 2));
+            const int py = pp / (G::PW1 / 2), px = 2 * (pp % (G::PW1 / 2));
+            float2 acc[2][4][G::C1 / 2];
 #pragma unroll
             for (int a = 0; a < 2; a++)
 #pragma unroll
-                for (int b = 0; b < 2; b++)
+                for (int b = 0; b < 4; b++)
 #pragma unroll
                     for (int c = 0; c < G::C1 / 2; c++) acc[a][b][c] = make_float2(0.f, 0.f);
             const float* ip = sm + G::S_IMG + g * G::IMG + ((2 * py) * G::W + 2 * px) * G::C;
 #pragma unroll 1
             for (int r = 0; r < 6; r++) {  // patch row r feeds output row dy with kernel row r-dy
-                float row[6 * G::C];
+                float row[8 * G::C];
 #pragma unroll
-                for (int i = 0; i < 6 * G::C; i++) row[i] = ip[r * G::W * G::C + i];
+                for (int i = 0; i < 8 * G::C; i++) row[i] = ip[r * G::W * G::C + i];
 #pragma unroll
                 for (int dy = 0; dy < 2; dy++) {
                     const int kh = r - dy;
@@ -135,38 +136,45 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
 #pragma unroll
                         for (int c = 0; c < G::C; c++) {
                             const float2* wp = reinterpret_cast<const float2*>(sm + G::S_W1 + ((kh * 5 + kw) * G::C + c) * G::C1);  // broadcast reads
-                            const float x0 = row[kw * G::C + c], x1 = row[(kw + 1) * G::C + c];
-                            const float2 v0 = make_float2(x0, x0), v1 = make_float2(x1, x1);
+                            float2 w[G::C1 / 2];
 #pragma unroll
-                            for (int co = 0; co < G::C1 / 2; co++) {
-                                const float2 w = wp[co];
-                                acc[dy][0][co] = __ffma2_rn(v0, w, acc[dy][0][co]);
-                                acc[dy][1][co] = __ffma2_rn(v1, w, acc[dy][1][co]);
+                            for (int co = 0; co < G::C1 / 2; co++) w[co] = wp[co];
+#pragma unroll
+                            for (int dx = 0; dx < 4; dx++) {
+                                const float x = row[(kw + dx) * G::C + c];
+                                const float2 v = make_float2(x, x);
+#pragma unroll
+                                for (int co = 0; co < G::C1 / 2; co++) acc[dy][dx][co] = __ffma2_rn(v, w[co], acc[dy][dx][co]);
                             }
                         }
                 }
             }
 #pragma unroll
-            for (int co = 0; co < G::C1 / 2; co++) {
-                const float mx = fmaxf(fmaxf(acc[0][0][co].x, acc[0][1][co].x), fmaxf(acc[1][0][co].x, acc[1][1][co].x));
-                const float my = fmaxf(fmaxf(acc[0][0][co].y, acc[0][1][co].y), fmaxf(acc[1][0][co].y, acc[1][1][co].y));
-                sm[G::S_P1 + g * G::P1 + pp * G::C1 + 2 * co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + 2 * co], 0.f);
-                sm[G::S_P1 + g * G::P1 + pp * G::C1 + 2 * co + 1] = fmaxf(my + sm[G::S_W1 + G::NW1 + 2 * co + 1], 0.f);
+            for (int h = 0; h < 2; h++) {  // the two pooled columns
+                float* op = sm + G::S_P1 + g * G::P1 + (py * G::PW1 + px + h) * G::C1;
+#pragma unroll
+                for (int co = 0; co < G::C1 / 2; co++) {
+                    const float mx = fmaxf(fmaxf(acc[0][2 * h][co].x, acc[0][2 * h + 1][co].x), fmaxf(acc[1][2 * h][co].x, acc[1][2 * h + 1][co].x));
+                    const float my = fmaxf(fmaxf(acc[0][2 * h][co].y, acc[0][2 * h + 1][co].y), fmaxf(acc[1][2 * h][co].y, acc[1][2 * h + 1][co].y));
+                    op[2 * co] = fmaxf(mx + sm[G::S_W1 + G::NW1 + 2 * co], 0.f);
+                    op[2 * co + 1] = fmaxf(my + sm[G::S_W1 + G::NW1 + 2 * co + 1], 0.f);
+                }
             }
         }
         __syncthreads();
-        // ---- conv2 + bias + ReLU + pool: item = (image, pooled position, 4 output channels)
-        for (int item = tid; item < imgs * G::PH2 * G::PW2 * 4; item += kGT) {
-            const int q = item & 3, t2 = item >> 2;
+        // ---- conv2 + bias + ReLU + pool: item = (image, pooled position, HALF of the 16 output channels): 2 x 2 conv outputs x 8
+        // channels, two 128-bit weight loads per (kw, c) feeding 8 packed FMA
+        for (int item = tid; item < imgs * G::PH2 * G::PW2 * 2; item += kGT) {
+            const int q = item & 1, t2 = item >> 1;
             const int g = t2 / (G::PH2 * G::PW2), pos = t2 % (G::PH2 * G::PW2);
             const int py = pos / G::PW2, px = pos % G::PW2;
-            float2 acc[2][2][2];
+            float2 acc[2][2][4];
 #pragma unroll
             for (int a = 0; a < 2; a++)
 #pragma unroll
                 for (int b = 0; b < 2; b++)
 #pragma unroll
-                    for (int c = 0; c < 2; c++) acc[a][b][c] = make_float2(0.f, 0.f);
+                    for (int c = 0; c < 4; c++) acc[a][b][c] = make_float2(0.f, 0.f);
             const float* ip = sm + G::S_P1 + g * G::P1 + ((2 * py) * G::PW1 + 2 * px) * G::C1;
 #pragma unroll 1
             for (int r = 0; r < 6; r++) {
@@ -181,20 +189,23 @@ __global__ void __launch_bounds__(kGT) guard_fp32_kernel(DeviceModel m, const fl
                     for (int kw = 0; kw < 5; kw++)
 #pragma unroll
                         for (int c = 0; c < G::C1; c++) {
-                            const float4 w = *reinterpret_cast<const float4*>(sm + G::S_W2 + ((kh * 5 + kw) * G::C1 + c) * G::C2 + 4 * q);
+                            const float4* wp = reinterpret_cast<const float4*>(sm + G::S_W2 + ((kh * 5 + kw) * G::C1 + c) * G::C2 + 8 * q);
+                            const float4 wa = wp[0], wb = wp[1];
+                            const float2 w0 = make_float2(wa.x, wa.y), w1 = make_float2(wa.z, wa.w), w2 = make_float2(wb.x, wb.y), w3 = make_float2(wb.z, wb.w);
                             const float x0 = row[kw * G::C1 + c], x1 = row[(kw + 1) * G::C1 + c];
                             const float2 v0 = make_float2(x0, x0), v1 = make_float2(x1, x1);
-                            const float2 wlo = make_float2(w.x, w.y), whi = make_float2(w.z, w.w);
-                            acc[dy][0][0] = __ffma2_rn(v0, wlo, acc[dy][0][0]); acc[dy][0][1] = __ffma2_rn(v0, whi, acc[dy][0][1]);
-                            acc[dy][1][0] = __ffma2_rn(v1, wlo, acc[dy][1][0]); acc[dy][1][1] = __ffma2_rn(v1, whi, acc[dy][1][1]);
+                            acc[dy][0][0] = __ffma2_rn(v0, w0, acc[dy][0][0]); acc[dy][0][1] = __ffma2_rn(v0, w1, acc[dy][0][1]);
+                            acc[dy][0][2] = __ffma2_rn(v0, w2, acc[dy][0][2]); acc[dy][0][3] = __ffma2_rn(v0, w3, acc[dy][0][3]);
+                            acc[dy][1][0] = __ffma2_rn(v1, w0, acc[dy][1][0]); acc[dy][1][1] = __ffma2_rn(v1, w1, acc[dy][1][1]);
+                            acc[dy][1][2] = __ffma2_rn(v1, w2, acc[dy][1][2]); acc[dy][1][3] = __ffma2_rn(v1, w3, acc[dy][1][3]);
                         }
                 }
             }
 #pragma unroll
-            for (int c = 0; c < 4; c++) {
+            for (int c = 0; c < 8; c++) {
                 auto at = [&](int a, int b) { return (c & 1) ? acc[a][b][c >> 1].y : acc[a][b][c >> 1].x; };
                 const float mx = fmaxf(fmaxf(at(0, 0), at(0, 1)), fmaxf(at(1, 0), at(1, 1)));
-                sm[G::S_P2 + g * G::FEAT + pos * G::C2 + 4 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 4 * q + c], 0.f);  // (h,w,c) flatten
+                sm[G::S_P2 + g * G::FEAT + pos * G::C2 + 8 * q + c] = fmaxf(mx + sm[G::S_W2 + G::NW2 + 8 * q + c], 0.f);  // (h,w,c) flatten
             }
         }
         __syncthreads();
