@@ -3,25 +3,28 @@
 // Replaces Session.run("input:0" -> "output/Softmax:0") (InferenceBolt.java:81-85) for the graded models
 // (conv5x5(6) -> pool -> conv5x5(16) -> pool -> 120 -> 84 -> 10 -> softmax; 28x28x1 and 32x32x3).
 //
-// Shape of the kernel (DESIGN.md "tensor-core kernel" has the numbers behind each choice):
-//   * one persistent CTA per SM; every fc weight lives in shared memory as pre-swizzled mma B fragments for the
-//     whole launch, conv weights live in registers of the warps that use them;
-//   * warps are specialised and pipelined through shared-memory rings with mbarriers, 8 images per ring slot:
-//       conv1 warps: stream fp32 NHWC rows from HBM (128-bit coalesced loads, 4 rows in flight per warp in registers),
-//                    convert to half precision into a 2-row private staging ring, build im2col A fragments with a
-//                    5-row sliding register window (each staged row is read once and feeds 5 kernel rows),
-//                    mma.sync m16n8k16, bias+ReLU+2x2 maxpool fused in registers (even/odd column tiles make the
-//                    pool thread-local), pooled rows -> p1 ring;
-//       conv2 warps: same sliding window over p1 rows, N=16, pool thread-local by tile-row permutation -> p2 ring;
-//       fc warps   : 16-image M tiles: 400(256)->120->84->10, bias+ReLU fused, then a quad-shuffle softmax /
-//                    argmax / top1-top2 margin, and the margin guard's compaction list.
-//   * the dense-layer fragments (121 KB) arrive by cp.async.bulk on an mbarrier; only the dense head waits for them;
-//   * why mma.sync is the default and tcgen05 the option (SIB_CONV1_UMMA): the contractions are N=6 and N=16 wide with
-//     K=75/150. A tcgen05 operand read from shared memory costs 4 KB per M128xK16 mma at the 128 B/clk shared-memory
-//     pipe (39-48 clk per mma measured, tools/tcgen05_probe2.cu) whether or not a sliding-window descriptor avoids the
-//     im2col copy; with the operand in TMEM the mma is fast (9 clk) but the im2col rows still pass through registers,
-//     and the variant built that way reaches 210 M img/s against 230 M here. Register-resident sliding
-//     windows feed mma.sync m16n8k16 at 557 TFLOP/s on this B200 (profiles/microbench_r01.jsonl).
+// Shape of the kernel (DESIGN.md 4.1 has the numbers behind each choice, profiles/ncu_tc_r02_notes.md the history):
+//   * one persistent CTA per SM, 20 warps in five warpgroups with their registers re-dealt by setmaxnreg (conv1 128,
+//     everyone else 48); dense weights and conv2's filter live in shared memory for the whole launch, conv1's filter in
+//     registers; 8 images per p1 ring slot, 16 per p2 buffer;
+//   * warps are specialised and pipelined through shared memory and TMEM with mbarriers:
+//       conv1 warps (12, mma.sync m16n8k16): stream fp32 NHWC rows from HBM (128-bit coalesced loads, 4 rows in flight
+//                    per warp in registers), convert to half precision into a 2-row private staging ring, build im2col A
+//                    fragments with a 5-row sliding register window (each staged row is read once and feeds 5 kernel
+//                    rows), bias+ReLU+2x2 maxpool fused in registers (even/odd column tiles make the pool thread-local),
+//                    pooled rows -> p1 ring; spans are claimed from a shared counter;
+//       conv2 (tcgen05.mma, sib_tc_conv2_umma.cuh): 2 x 3 worker warps write every p1 row into TMEM once (tcgen05.st), an
+//                    issuer warp adds it into the accumulators of the five output rows it touches (M128 x N32 x K16,
+//                    A and D in TMEM, the stacked filter rows in shared memory), the workers pool the accumulators out
+//                    of TMEM (tcgen05.ld) straight into p2 in the dense head's operand layout;
+//       dense head (tcgen05.mma, sib_tc_fc_umma.cuh): transposed -- the weights are the M = 128 operand, a pair's 16 images
+//                    N; epilogues on the workers and the head warp; softmax / argmax / top1-top2 margin and the margin
+//                    guard's compaction list on the head warp.
+//   * the dense-layer operands (119 KB) arrive by cp.async.bulk on an mbarrier; only the dense head waits for them;
+//   * conv1 stays on mma.sync: its N = 6, K = 75 contraction has no cheap operand path to tcgen05 -- from shared memory an
+//     M128 x K16 operand costs 39-48 clk per mma, through registers (tcgen05.st: SIB_CONV1_UMMA, 208 M img/s) the im2col
+//     rows cost more instructions than the mma save, and tcgen05.cp builds them exactly but at 64 clk per copy, unoverlapped
+//     (tools/tcgen05_probe2/3.cu). -DSIB_CONV2_UMMA=0 builds the round-1 kernel (everything on mma.sync, 229 M img/s).
 //
 // Operand type is a template parameter: __half (default: 11-bit significand, max logit error 2e-2 on the presets)
 // or __nv_bfloat16 (8-bit significand, ~1e-1). Accumulation is always fp32.
