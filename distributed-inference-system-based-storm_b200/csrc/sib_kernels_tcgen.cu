@@ -119,21 +119,30 @@ __global__ void __launch_bounds__(kGT) forward_tcgen_kernel(const __grid_constan
                     float acc[8][4];
 #pragma unroll
                     for (int n8 = 0; n8 < 8; n8++) acc[n8][0] = acc[n8][1] = acc[n8][2] = acc[n8][3] = 0.f;
-                    for (int kh = 0; kh < KH; kh++) {
-                        const uint16_t* a_lo = r0 + kh * W * C + 2 * t;
-                        const uint16_t* a_hi = a_lo + W * C;
-                        for (int ks = 0; ks < KS; ks++) {
-                            uint32_t a[4];
-                            a[0] = ld_pair(a_lo + ks * 16, aligned); a[1] = ld_pair(a_hi + ks * 16, aligned);
-                            a[2] = ld_pair(a_lo + ks * 16 + 8, aligned); a[3] = ld_pair(a_hi + ks * 16 + 8, aligned);
-                            const uint32_t* bp = wsm + ((kh * KS + ks) * NT) * 64 + lane * 2;
-#pragma unroll
-                            for (int n8 = 0; n8 < 8; n8++)
-                                if (n8 < NT) {
-                                    const uint2 b = *reinterpret_cast<const uint2*>(bp + n8 * 64);
-                                    GOps<T>::mma(acc[n8], a, b.x, b.y);
-                                }
+                    // (kernel row, K step) pairs in one flat loop, the next step's A fragment loaded before this step's mma:
+                    // the loads then have NT mma to land under (+3% on the wide presets: the loop is not bound by them)
+                    const uint16_t* a_lo = r0 + 2 * t;
+                    const int steps = KH * KS, wrap = W * C - KS * 16;
+                    uint32_t a[4], an[4];
+                    a[0] = ld_pair(a_lo, aligned); a[1] = ld_pair(a_lo + W * C, aligned);
+                    a[2] = ld_pair(a_lo + 8, aligned); a[3] = ld_pair(a_lo + W * C + 8, aligned);
+                    int ks = 0;
+                    for (int st = 0; st < steps; st++) {
+                        a_lo += 16;
+                        if (++ks == KS) { ks = 0; a_lo += wrap; }
+                        if (st + 1 < steps) {
+                            an[0] = ld_pair(a_lo, aligned); an[1] = ld_pair(a_lo + W * C, aligned);
+                            an[2] = ld_pair(a_lo + 8, aligned); an[3] = ld_pair(a_lo + W * C + 8, aligned);
                         }
+                        const uint32_t* bp = wsm + (st * NT) * 64 + lane * 2;
+#pragma unroll
+                        for (int n8 = 0; n8 < 8; n8++)
+                            if (n8 < NT) {
+                                const uint2 b = *reinterpret_cast<const uint2*>(bp + n8 * 64);
+                                GOps<T>::mma(acc[n8], a, b.x, b.y);
+                            }
+#pragma unroll
+                        for (int i = 0; i < 4; i++) a[i] = an[i];
                     }
                     // epilogue: vertical max in the thread, horizontal max with the lane of the next column, + bias, ReLU
                     const int col = 8 * j + g;
