@@ -297,7 +297,35 @@ struct TcParams {
     int32_t* count;
     float tau;
     float* dbg;      // may be null: CTA 0 dumps p1/p2/h1/h2 of its first 16 images (tests)
+    int rounds;      // SIB_SPREAD_TAIL: rounds in which every CTA runs a whole pair (set by launch_inst from n and the grid)
+    int per;         //                  images per CTA in the round after them (0: the full rounds took everything)
 };
+
+// Which images are the Qi-th pair of this CTA: [base, lim), at most kPair of them; false = the CTA has no Qi-th pair.
+// Whole pairs are dealt round-robin (pair = blockIdx.x + Qi * gridDim.x). SIB_SPREAD_TAIL cuts what is left after the
+// last round that fills every CTA into equal runs of images, one run per CTA: the last round then costs every CTA the
+// same fraction of a pair instead of a whole pair on some CTAs and nothing on the rest (65 536 images: 100 of 148 CTAs
+// ran a 28th pair), and a launch of fewer images than 16 x the SM count is spread over all the CTAs it can use (16 images:
+// 16 CTAs with one image each, not one CTA walking 16 images through its pipeline).
+#ifndef SIB_SPREAD_TAIL
+#define SIB_SPREAD_TAIL SIB_CONV2_UMMA
+#endif
+__device__ __forceinline__ bool pair_images(const TcParams& P, int Qi, int& base, int& lim) {
+#if SIB_SPREAD_TAIL
+    if (Qi < P.rounds) {
+        base = (blockIdx.x + Qi * gridDim.x) * kPair;
+        lim = base + kPair;
+        return true;
+    }
+    base = P.rounds * (int)gridDim.x * kPair + blockIdx.x * P.per;
+    lim = min(base + P.per, P.n);
+    return Qi == P.rounds && base < lim;
+#else
+    base = (blockIdx.x + Qi * gridDim.x) * kPair;
+    lim = min(base + kPair, P.n);
+    return base < P.n;
+#endif
+}
 
 #if SIB_CONV1_UMMA || SIB_CONV2_UMMA
 #include "sib_tc_umma.cuh"
@@ -331,23 +359,23 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
     const float* biasp = reinterpret_cast<const float*>(P.wpack + N::W_BIAS);
     const float bias0 = biasp[2 * t], bias1 = biasp[2 * t + 1];
 
-    const int nPairs = (P.n + kPair - 1) / kPair;
-    // spans in CTA order: local slot lq = 0,1,2.. ; slot lq -> pair Qi = lq/2 (global pair blockIdx.x + Qi*gridDim.x)
-    auto span_src = [&](int gs, int& img0, bool& valid) {
+    // spans in CTA order: local slot lq = 0,1,2.. ; slot lq -> the CTA's pair Qi = lq/2 (pair_images); lim = one past the
+    // pair's last image
+    auto span_src = [&](int gs, int& img0, int& lim, bool& valid) {
         const int lq = gs / N::SPANS;
-        const int pair = blockIdx.x + (lq >> 1) * gridDim.x;
-        valid = pair < nPairs;
-        img0 = pair * kPair + (lq & 1) * kG;
+        int base;
+        valid = pair_images(P, lq >> 1, base, lim);
+        img0 = base + (lq & 1) * kG;
     };
     // Every lane copies one 16-byte chunk of the span row; lanes past the last chunk repeat it (same bytes to the
     // same address), which keeps the whole staging path free of divergent branches.
     const int chunk = lane < N::NCHUNK ? lane : N::NCHUNK - 1;
-    auto chunk_ptr = [&](int img0, int s) -> const float* {
+    auto chunk_ptr = [&](int img0, int s, int lim) -> const float* {
         const int p0 = 32 * s;
         const int u_start = (p0 / N::OW1) * N::W + p0 % N::OW1;
         const int F0 = u_start * N::C + 4 * chunk;
         int img = img0 + F0 / N::ROWF;
-        img = min(img, P.n - 1);  // tail slots re-read the last image; their outputs are never written
+        img = min(img, lim - 1);  // tail slots re-read the pair's last image; their outputs are never written
         return P.in + (size_t)img * N::IMG + F0 % N::ROWF;
     };
 
@@ -361,11 +389,11 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         return __shfl_sync(0xffffffffu, v, 0);
     };
     int gs = SIB_DYN_SPANS ? claim() : cw;
-    int img0;
+    int img0, lim;
     bool valid;
-    span_src(gs, img0, valid);
+    span_src(gs, img0, lim, valid);
     if (!valid) return;
-    const float* src = chunk_ptr(img0, gs % N::SPANS);
+    const float* src = chunk_ptr(img0, gs % N::SPANS, lim);
     float4 preA[kBR], preB[kBR];  // REG_STAGE: two batches of kBR consecutive rows, one 16-byte chunk per lane
     if constexpr (N::REG_STAGE) {
 #pragma unroll
@@ -385,18 +413,18 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         const int buf = lq % N::NB1, use = lq / N::NB1;
         uint16_t* p1 = reinterpret_cast<uint16_t*>(smem + N::S_P1) + buf * N::P1_BUF;
         // next span (for the tail prefetch)
-        int n_img0;
+        int n_img0, n_lim;
         bool n_valid;
         const int n_gs = SIB_DYN_SPANS ? claim() : gs + kConv1Warps;
-        span_src(n_gs, n_img0, n_valid);
-        const float* n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS) : src;
+        span_src(n_gs, n_img0, n_lim, n_valid);
+        const float* n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS, n_lim) : src;
         // A span whose first column already lies past the last image has nothing to compute (the tail of a batch:
         // with 1 image in a launch, 13 of the pair's 14 spans). It only keeps the slot protocol going. Image indices
         // grow with gs, so every later span of this warp is empty as well and the prefetch state no longer matters.
-        if ((SIB_DIAG_SKIP & 1) || (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= P.n)) {
+        if ((SIB_DIAG_SKIP & 1) || (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= lim)) {
             mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
             mbar_arrive(&p1_full[buf]);
-            gs = n_gs; valid = n_valid; src = n_src; img0 = n_img0;
+            gs = n_gs; valid = n_valid; src = n_src; img0 = n_img0; lim = n_lim;
             continue;
         }
 
@@ -532,6 +560,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         valid = n_valid;
         src = n_src;
         img0 = n_img0;
+        lim = n_lim;
     }
 }
 
@@ -1101,9 +1130,19 @@ int launch_inst(const TcParams& p, cudaStream_t st) {
         }))
         return rc;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    TcParams q = p;
+#if SIB_SPREAD_TAIL
+    // one CTA per SM, or per image when there are fewer images than SMs; the stage dump is CTA 0's first pair, so a
+    // launch that dumps runs on one CTA (grid 1: whole pairs in order, then the remainder -- the plain order)
+    const int grid = DBG ? 1 : (p.n < sms ? p.n : sms);
+    q.rounds = p.n / kPair / grid;
+    const int rem = p.n - q.rounds * grid * kPair;  // < grid * kPair
+    q.per = (rem + grid - 1) / grid;
+#else
     const int pairs = (p.n + kPair - 1) / kPair;
     const int grid = pairs < sms ? pairs : sms;
-    forward_tc_kernel<N, T, DBG><<<grid, kThreadsTc, N::S_TOTAL, st>>>(p);
+#endif
+    forward_tc_kernel<N, T, DBG><<<grid, kThreadsTc, N::S_TOTAL, st>>>(q);
     return (int)cudaGetLastError();
 }
 

@@ -126,9 +126,9 @@ struct U2Bars {  // shared-memory addresses of the stage's barriers
 // does slot lq of this CTA hold work? (the launch's last pair may be half empty)
 template <typename N>
 __device__ __forceinline__ int conv2u_slot(const TcParams& P, int lq) {  // -1: past the end, 0: empty slot, 1: work
-    const int pair = blockIdx.x + (lq >> 1) * gridDim.x;
-    if (pair >= (P.n + kPair - 1) / kPair) return -1;
-    return (SIB_SKIP_EMPTY && pair * kPair + (lq & 1) * kG >= P.n) ? 0 : 1;
+    int base, lim;
+    if (!pair_images(P, lq >> 1, base, lim)) return -1;
+    return (SIB_SKIP_EMPTY && base + (lq & 1) * kG >= lim) ? 0 : 1;
 }
 
 template <typename N, typename T, bool DBG, int STAGE>
@@ -154,8 +154,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         return;
     }
     if (nimg == 0) {  // no conv2 columns in this quadrant (mnist, q = 2): only the dense head's epilogues
-        const int nPairs = (P.n + kPair - 1) / kPair;
-        for (int Qi = 0; (int)(blockIdx.x + Qi * gridDim.x) < nPairs; Qi++) {
+        for (int Qi = 0; conv2u_slot<N>(P, 2 * Qi) >= 0; Qi++) {
             if (fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi);
             if (fc2_mine) fcu_epilogue<N, T, DBG, 2>(P, smem, q, lane, tmem, Qi);
         }

@@ -83,12 +83,11 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
     const uint32_t d = tmem + kTmF;
     float* scratch = reinterpret_cast<float*>(smem + N::S_FCS);  // [16 images][10 classes]
     const float b3 = lane < 10 ? reinterpret_cast<const float*>(smem + N::S_BIAS)[248 + lane] : 0.f;
-    const int nPairs = (P.n + kPair - 1) / kPair;
     mbar_wait_s(F.fcw, 0);  // the weight image is in
     if (SIB_DIAG_SKIP & 4) return;
     for (int Qi = 0;; Qi++) {
-        const int pair = blockIdx.x + Qi * gridDim.x;
-        if (pair >= nPairs) break;
+        int base, lim;
+        if (!pair_images(P, Qi, base, lim)) break;
         const int buf = Qi % N::NP2, use = Qi / N::NP2;
         const uint32_t ph = Qi & 1;
         // ---- fc1
@@ -134,8 +133,8 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
             for (int n = 0; n < 16; n++) scratch[n * 10 + lane] = x[n] + b3;
         }
         __syncwarp();
-        const int img = pair * kPair + lane;
-        if (lane < 16 && img < P.n) {  // one image per lane: softmax, argmax (first maximum), top1 - top2 margin
+        const int img = base + lane;
+        if (lane < 16 && img < lim) {  // one image per lane: softmax, argmax (first maximum), top1 - top2 margin
             float lg[10];
 #pragma unroll
             for (int c = 0; c < 10; c++) lg[c] = scratch[lane * 10 + c];
