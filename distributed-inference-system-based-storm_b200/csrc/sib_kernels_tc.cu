@@ -938,7 +938,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1) forward_tc_kernel(TcParams P) {
 #endif
             for (int i = 0; i < N::NB1; i++) {
                 mbar_init(&bars[N::B_P1F + i], SIB_CONV1_UMMA ? 256 : N::SPANS * 32);  // p1_full : every conv1 lane working on the slot
-                mbar_init(&bars[N::B_P1E + i], kConv2Arrivals<N>());  // p1_empty: every lane of every conv2 tile | worker
+                mbar_init(&bars[N::B_P1E + i], (SIB_CONV2_UMMA ? 2 : 1) * kConv2Arrivals<N>());  // p1_empty: every lane of every conv2 tile | of both worker sets
             }
             for (int i = 0; i < 2; i++) {
                 mbar_init(&bars[N::B_P2F + i], (SIB_CONV2_UMMA ? 4 : 2) * kConv2Arrivals<N>());  // p2_full : two slots of conv2 tiles | both worker sets

@@ -147,7 +147,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
     const int nlive = nimg * N::OW2;
     if (SIB_DIAG_SKIP & 4) {  // diagnostic: conv1 alone (the p1 slots are recycled unread)
         for (int lq = 0; conv2u_slot<N>(P, lq) >= 0; lq++) {
-            if (nimg == 0 || set != 0) continue;
+            if (nimg == 0) continue;
             mbar_wait_s(B.p1_full + (lq % N::NB1) * 8, (lq / N::NB1) & 1);
             mbar_arrive_s(B.p1_empty + (lq % N::NB1) * 8);
         }
@@ -183,7 +183,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
         const int buf2 = Qi % N::NP2, use2 = Qi / N::NP2;
         mbar_wait_s(B.p1_full + buf1 * 8, use1 & 1);
         if (work == 0) {  // nothing to compute, keep the slot protocol going
-            if (set == 0) mbar_arrive_s(B.p1_empty + buf1 * 8);
+            mbar_arrive_s(B.p1_empty + buf1 * 8);
             mbar_arrive_s(B.p2_full + buf2 * 8);
             continue;
         }
@@ -212,7 +212,10 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
             tc5_fence_before();
             mbar_arrive_s(B.a_full + rp * 8);
         }
-        if (((U::RP - 1) & 1) == set) mbar_arrive_s(B.p1_empty + buf1 * 8);  // the set that stored the slot's last rows
+        // Both sets hand the slot back, each after its own last load from it. (Only the set that stored the slot's last
+        // rows used to: the other set is at most a tile behind and conv1 needs ~1 us to reach the first row it might still
+        // want, so no run ever showed a difference -- but nothing in the protocol ruled it out.)
+        mbar_arrive_s(B.p1_empty + buf1 * 8);
         const bool head_due = (lq & 1) == 0 && Qi > 0;  // the previous pair's dense head
         if (head_due && fc1_mine) fcu_epilogue<N, T, DBG, 1>(P, smem, q, lane, tmem, Qi - 1);
         // first write into this pair's p2 buffer: fc1 of the pair that used it before must have read it (its mma ran
