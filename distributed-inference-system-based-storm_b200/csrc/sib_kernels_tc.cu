@@ -154,8 +154,18 @@ struct Net {
     // tcgen05 dense head: p2 / h1 / h2 are B operands (K-major, no swizzle: [img/8][k/8][img%8][k%8]), the weights A operands
     // ([m/8][k/8][m%8][k%8]); *_SBO = bytes between 8-row groups, 128 bytes between K chunks
     static constexpr int F1_SBO = FEAT / 8 * 128, F2_SBO = 128 / 8 * 128, F3_SBO = 96 / 8 * 128;
+    // The B operands (p2, h1, h2) are WRITTEN by warps whose lanes differ in the K chunk: with the chunks 128 bytes
+    // apart every lane of a store hit the same four banks (p2's 16-byte stores took 22 wavefronts instead of 4, the
+    // head's 2-byte stores 4 instead of 1: 12% of the kernel's shared-memory wavefronts, profiles/ncu_tc_r02_final.txt).
+    // 144 bytes between K chunks moves consecutive chunks to consecutive 16-byte bank groups; the descriptor's leading
+    // byte offset takes any multiple of 16.
+#ifndef SIB_BK
+#define SIB_BK 144
+#endif
+    static constexpr int BK = SIB_BK;                                     // bytes between the K chunks of a B operand
+    static constexpr int P2_SBO = FEAT / 8 * BK, H1_SBO = 128 / 8 * BK, H2_SBO = 96 / 8 * BK;  // bytes between its 8-image groups
     static constexpr int F1_GROUPS = 15, F2_GROUPS = 11, F3_GROUPS = 2;   // row groups that are stored (120 | 84 -> 88 | 10 -> 16 rows)
-    static constexpr int P2_BUF = SIB_CONV2_UMMA ? kPair * FEAT : kPair * P2_STRIDE;
+    static constexpr int P2_BUF = SIB_CONV2_UMMA ? 2 * P2_SBO / 2 : kPair * P2_STRIDE;  // halves
     static constexpr int DBG_P2 = kPair * P2_STRIDE;               // the stage dump keeps the padded [img][feature] layout
     static constexpr int H1_STRIDE = 136, H2_STRIDE = 104;
     // Input staging. H % 8 == 0: two register batches of 4 rows (2 scoreboard slots, no shared-memory cost).
@@ -190,7 +200,7 @@ struct Net {
     static constexpr int S_H1 = S_P2 + NP2 * P2_BUF * 2;
     static constexpr int NHB = SIB_FC_IN_CONV2 ? 2 : 1;                    // h1/h2 buffers: dense heads of two pairs may overlap
     static constexpr int S_H2 = SIB_CONV2_UMMA ? S_H1 : S_H1 + NHB * kPair * H1_STRIDE * 2;          // tcgen05 head: h2 overlays h1
-    static constexpr int S_FCS = SIB_CONV2_UMMA ? S_H1 + 2 * F2_SBO : S_H2 + NHB * kPair * H2_STRIDE * 2;  // tcgen05 head: logits [16][10] fp32, lane <-> image transpose
+    static constexpr int S_FCS = SIB_CONV2_UMMA ? S_H1 + 2 * H1_SBO : S_H2 + NHB * kPair * H2_STRIDE * 2;  // tcgen05 head: logits [16][10] fp32, lane <-> image transpose
     static constexpr int S_RING = S_FCS + (SIB_CONV2_UMMA ? kPair * 10 * 4 : 0);
     static constexpr int STAGE_ROW = NCHUNK * 16;                          // bytes of one fp32 span row
     static constexpr int URING_ROW = 2 * W * C + 16;                       // halves: Umma<N>::UROW

@@ -166,8 +166,8 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
     const int odd = lane & 1;                        // the pool pair is (lane, lane ^ 1); this lane stores channels 8*odd..+7
     const uint32_t offA = smem_u32(smem + N::S_P1) + (imgl * N::P1_IMG + ow * N::C1) * 2;            // + buf, + row
     const int o2 = imgl * N::P2_STRIDE + (ow >> 1) * N::C2 + odd * 8;  // stage dump: padded [img][feature] layout
-    // p2 is the dense head's B operand: [img/8][k/8][img%8][k%8]; this lane's 8 channels are one 16-byte chunk of it
-    const uint32_t offP2 = smem_u32(smem + N::S_P2) + ((ow >> 1) * 2 + odd) * 128 + imgl * 16;
+    // p2 is the dense head's B operand: [img/8][k/8][img%8][k%8], BK bytes per k/8; this lane's 8 channels are one 16-byte chunk of it
+    const uint32_t offP2 = smem_u32(smem + N::S_P2) + ((ow >> 1) * 2 + odd) * N::BK + imgl * 16;
     const uint32_t tm_lane = tmem + ((uint32_t)(q * 32) << 16);
     // The bias rides in the mma: K slots 30, 31 of every A row hold 1.0 and kernel row 0's B tile holds the bias there,
     // split into a half-precision head and tail (b = hi + lo to ~22 bits); every output row meets kernel row 0 once.
@@ -188,7 +188,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
             continue;
         }
         const uint32_t src0 = offA + buf1 * N::P1_BUF * 2;
-        const uint32_t p2 = offP2 + buf2 * N::P2_BUF * 2 + (lq & 1) * N::F1_SBO;
+        const uint32_t p2 = offP2 + buf2 * N::P2_BUF * 2 + (lq & 1) * N::P2_SBO;
         const bool dump = DBG && P.dbg && blockIdx.x == 0 && Qi == 0;
         const uint32_t par = seq & 1;
 
@@ -242,7 +242,7 @@ __device__ __forceinline__ void conv2u_worker(const TcParams& P, unsigned char* 
                 uint4 pk;
                 pk.x = Ops<T>::pack(v[0], v[1]); pk.y = Ops<T>::pack(v[2], v[3]);
                 pk.z = Ops<T>::pack(v[4], v[5]); pk.w = Ops<T>::pack(v[6], v[7]);
-                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(p2 + j * N::PW2 * 256), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w) : "memory");
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(p2 + j * N::PW2 * 2 * N::BK), "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w) : "memory");
                 if (dump) {
                     float* dg = P.dbg + 2 * kG * N::PH1 * N::P1_ROW + (lq & 1) * kG * N::P2_STRIDE + o2 + j * N::PW2 * N::C2;
 #pragma unroll

@@ -48,7 +48,7 @@ constexpr int kTmF = 480;  // TMEM columns of the head's accumulator (16): D1, t
 template <typename N, typename T, bool DBG, int STAGE>
 __device__ __forceinline__ void fcu_epilogue(const TcParams& P, unsigned char* smem, int q, int lane, uint32_t tmem, int Qi) {
     const FcBars<N> F(smem);
-    constexpr int REAL = STAGE == 1 ? 120 : 84, SBO = STAGE == 1 ? N::F2_SBO : N::F3_SBO;
+    constexpr int REAL = STAGE == 1 ? 120 : 84, KPAD = STAGE == 1 ? 128 : 96, SBO = STAGE == 1 ? N::H1_SBO : N::H2_SBO;
     const int f = q * 32 + lane;
     const float b = f < REAL ? reinterpret_cast<const float*>(smem + N::S_BIAS)[(STAGE == 1 ? 24 : 152) + f] : 0.f;
     mbar_wait_s(F.f_full + (STAGE - 1) * 8, Qi & 1);
@@ -57,8 +57,8 @@ __device__ __forceinline__ void fcu_epilogue(const TcParams& P, unsigned char* s
     tmem_ld16(tmem + ((uint32_t)(q * 32) << 16) + kTmF, v);
     tmem_wait_ld();
     tc5_fence_before();
-    const uint32_t dst = smem_u32(smem + (STAGE == 1 ? N::S_H1 : N::S_H2)) + (f >> 3) * 128 + (f & 7) * 2;
-    if (f < SBO / 16) {  // features past the padded K do not exist in the next layer's operand
+    const uint32_t dst = smem_u32(smem + (STAGE == 1 ? N::S_H1 : N::S_H2)) + (f >> 3) * N::BK + (f & 7) * 2;
+    if (f < KPAD) {  // features past the padded K do not exist in the next layer's operand
 #pragma unroll
         for (int n = 0; n < 16; n++) {
             const float x = f < REAL ? fmax_nan(v[n] + b, 0.f) : 0.f;
@@ -96,7 +96,7 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
         if (elect_one()) {
 #pragma unroll 1
             for (int ks = 0; ks < N::KS1; ks++)
-                umma_ss(d, umma_desc(a1 + ks * 256, 128, N::F1_SBO), umma_desc(b_p2 + buf * N::P2_BUF * 2 + ks * 256, 128, N::F1_SBO), idesc, ks > 0);
+                umma_ss(d, umma_desc(a1 + ks * 256, 128, N::F1_SBO), umma_desc(b_p2 + buf * N::P2_BUF * 2 + ks * 2 * N::BK, N::BK, N::P2_SBO), idesc, ks > 0);
             umma_commit_s(F.f_full);
             umma_commit_s(B.p2_empty + buf * 8);  // the pair's features have been read
         }
@@ -108,7 +108,7 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
         if (elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < 8; ks++)
-                umma_ss(d, umma_desc(a2 + ks * 256, 128, N::F2_SBO), umma_desc(b_h1 + ks * 256, 128, N::F2_SBO), idesc, ks > 0);
+                umma_ss(d, umma_desc(a2 + ks * 256, 128, N::F2_SBO), umma_desc(b_h1 + ks * 2 * N::BK, N::BK, N::H1_SBO), idesc, ks > 0);
             umma_commit_s(F.f_full + 8);
         }
         __syncwarp();
@@ -118,7 +118,7 @@ __device__ __forceinline__ void fcu_head(const TcParams& P, unsigned char* smem,
         if (elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < 6; ks++)
-                umma_ss(d, umma_desc(a3 + ks * 256, 128, N::F3_SBO), umma_desc(b_h2 + ks * 256, 128, N::F3_SBO), idesc, ks > 0);
+                umma_ss(d, umma_desc(a3 + ks * 256, 128, N::F3_SBO), umma_desc(b_h2 + ks * 2 * N::BK, N::BK, N::H2_SBO), idesc, ks > 0);
             umma_commit_s(F.f_full + 16);
         }
         __syncwarp();

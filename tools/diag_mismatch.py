@@ -1,8 +1,13 @@
+"""Which images of the 2^20-image sweep get another argmax than the CPU path, and how close their fp32 top-2 logits are.
+
+    python tools/diag_mismatch.py [preset] > profiles/mismatch_<preset>.jsonl      (GPU box)
+"""
 import os, sys, json
-sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/oracle')
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'oracle'))
 import numpy as np
 import oracle, sib_b200 as sib
-m = sib.modelspec.make_preset("mnist-lenet5")
+m = sib.modelspec.make_preset(sys.argv[1] if len(sys.argv) > 1 else "mnist-lenet5")
 blob = m.to_blob()
 n = 1 << 20
 x = np.concatenate([sib.modelspec.synthetic_images(m, bi, 65536) for bi in range(n // 65536)])
@@ -13,7 +18,7 @@ with sib.native.Engine(blob, max_batch=65536) as e:
     got = np.concatenate([e.forward_sync(x[i:i + 65536])[2] for i in range(0, n, 65536)])
     lgt = np.concatenate([e.forward_sync(x[i:i + 65536])[1] for i in range(0, n, 65536)])
 bad = np.nonzero(got != ref)[0]
-print("mismatches", bad)
+print(json.dumps({"preset": m.name, "images": n, "mismatches": [int(i) for i in bad]}))
 with sib.native.Engine(blob, max_batch=65536, precision=sib.native.PREC_FP32) as e32, sib.native.Engine(blob, max_batch=65536, guard=False) as e16:
     for i in bad:
         xi = x[i:i + 1]
