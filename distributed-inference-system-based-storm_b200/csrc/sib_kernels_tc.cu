@@ -422,16 +422,25 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         const int s = gs % N::SPANS, lq = gs / N::SPANS;
         const int buf = lq % N::NB1, use = lq / N::NB1;
         uint16_t* p1 = reinterpret_cast<uint16_t*>(smem + N::S_P1) + buf * N::P1_BUF;
-        // next span (for the tail prefetch)
-        int n_img0, n_lim;
-        bool n_valid;
-        const int n_gs = SIB_DYN_SPANS ? claim() : gs + kConv1Warps;
-        span_src(n_gs, n_img0, n_lim, n_valid);
-        const float* n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS, n_lim) : src;
+        // Next span (for the tail prefetch). The claim's atomic is issued here and its answer is taken a few rows into
+        // the span (resolve_next): taken at once, its latency sat on every span's critical path -- 5.6% of the conv1
+        // warps' stall samples (profiles/ncu_tc_r02_final.txt, the atomicAdd line).
+        int n_img0, n_lim, n_gs = 0, n_raw = 0;
+        bool n_valid = false;
+        const float* n_src = src;
+        if (SIB_DYN_SPANS && lane == 0) n_raw = (int)atomicAdd(span_ctr, 1u);
+        auto resolve_next = [&]() {
+            n_gs = SIB_DYN_SPANS ? __shfl_sync(0xffffffffu, n_raw, 0) : gs + kConv1Warps;
+            span_src(n_gs, n_img0, n_lim, n_valid);
+            n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS, n_lim) : src;
+        };
+        constexpr int kResolveAt = N::REG_STAGE ? 3 : -1;  // the cp.async ring asks for n_valid from its first row on
+        if (kResolveAt < 0) resolve_next();
         // A span whose first column already lies past the last image has nothing to compute (the tail of a batch:
         // with 1 image in a launch, 13 of the pair's 14 spans). It only keeps the slot protocol going. Image indices
         // grow with gs, so every later span of this warp is empty as well and the prefetch state no longer matters.
         if ((SIB_DIAG_SKIP & 1) || (SIB_SKIP_EMPTY && img0 + (32 * s) / N::OW1 >= lim)) {
+            if (kResolveAt >= 0) resolve_next();
             mbar_wait(&p1_empty[buf], (use & 1) ^ 1);
             mbar_arrive(&p1_full[buf]);
             gs = n_gs; valid = n_valid; src = n_src; img0 = n_img0; lim = n_lim;
@@ -507,6 +516,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
         // so neither the shared-memory round trip nor the mma dependency chains sit on the critical path.
 #pragma unroll
         for (int h = 0; h < N::H; h++) {
+            if (h == kResolveAt) resolve_next();
             if (h + 1 < N::H) stage_row(h + 1);
             // the accumulators start at the bias (same for the 4 positions of a pool window, so max(.) + b == max(. + b))
             float cE[4], cO[4];
