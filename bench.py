@@ -411,6 +411,35 @@ def run_ours(args):
         tc_ms = statistics.median(ev2[i].elapsed_time(ev2[i + 1]) for i in range(args.steps))
         eng0.close()
 
+    # ---- the same kernel at R x B images per launch (N = 1 only): a launch costs ~17 us of set-up, fill and drain
+    # whatever its size (profiles/fixed_cost_r02_*.jsonl), so this is what the kernel does once that is amortised. The
+    # R rotating batches become one contiguous input (R x B images >> L2), read from HBM by every launch.
+    large = None
+    if tc_ms is not None and world == 1 and not os.environ.get("SIB_BENCH_NO_LARGE"):
+        try:
+            BL = R * B
+            x_big = torch.cat(d_in, dim=0)
+            p_big = torch.empty((BL, model.n_classes), dtype=torch.float32, device=dev)
+            a_big = torch.empty(BL, dtype=torch.int32, device=dev)
+            engL = native.Engine(blob, device=dev, task_index=rank, max_batch=BL, precision=prec, n_slots=1, guard=False)
+            with torch.cuda.stream(stream):
+                for _ in range(3):
+                    engL.forward_device(x_big.data_ptr(), BL, p_big.data_ptr(), 0, a_big.data_ptr(), stream.cuda_stream)
+                ev3 = [torch.cuda.Event(enable_timing=True) for _ in range(11)]
+                torch.cuda.synchronize()
+                ev3[0].record(stream)
+                for i in range(10):
+                    engL.forward_device(x_big.data_ptr(), BL, p_big.data_ptr(), 0, a_big.data_ptr(), stream.cuda_stream)
+                    ev3[i + 1].record(stream)
+                torch.cuda.synchronize()
+            big_ms = statistics.median(ev3[i].elapsed_time(ev3[i + 1]) for i in range(10))
+            engL.close()
+            assert abs(float(p_big.sum().item()) - BL) < 1e-2 * BL
+            large = {"images_per_launch": BL, "kernel_ms": big_ms, "launches": 10}
+            del x_big, p_big, a_big
+        except Exception as ex:  # never lose the bench line to this leg
+            large = {"error": str(ex)[:200]}
+
     # ---- T1: host buffers through the C ABI. Like a Storm worker with several executors feeding one GPU, a few
     # host threads submit chunks of fp32 images (sib_submit_f32 copies them into the pinned slot outside the engine
     # lock; ctypes releases the GIL for the call) while this thread polls results.
@@ -561,7 +590,8 @@ def run_ours(args):
                      "kernel_ms": k_ms, "step_ms": step_med,
                      "guard_kernel_ms": (step_med - tc_ms) if tc_ms is not None else 0.0,
                      "algorithmic_bytes_per_image": bpi, "images_per_launch": B,
-                     "flops_per_image": model.flops_per_image()},
+                     "flops_per_image": model.flops_per_image(),
+                     "large_launch": _large_launch(large, roof, bpi, model.flops_per_image())},
         "clocks": clocks, "guard_recomputed_images": int(guard_n),
         # (counted on the submit/poll path, i.e. over the e2e leg's images)
         "guard_recomputed_fraction": (float(guard_n) / float(B * (e2e["steps"] + max(1, min(args.warmup, 3)))) if e2e else None),
@@ -584,6 +614,15 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _large_launch(large, roof, bpi, fpi):
+    """roofline of the dominant kernel at the large launch size, against the same peak as roofline.frac"""
+    if not large or "kernel_ms" not in large:
+        return large
+    per = fpi * 1e-12 if roof["bound"] == "tensor" else bpi * 1e-9
+    ach = large["images_per_launch"] * per / (large["kernel_ms"] * 1e-3)
+    return {**large, "achieved": ach, "unit": roof["unit"], "frac": ach / roof["peak"]}
 
 
 def _poll_count(eng, timeout_us):
