@@ -67,6 +67,10 @@ namespace {
 #ifndef SIB_L2_PREFETCH
 #define SIB_L2_PREFETCH 0   // conv1 (mma.sync path): prefetch.global.L2 of the row 2*PD rows ahead (measured: 218 M img/s with, 223 M without)
 #endif
+#ifndef SIB_L2_BULK_PREFETCH
+#define SIB_L2_BULK_PREFETCH 0   // conv1: one cp.async.bulk.prefetch.L2 per span for the images the warp's next span reads
+                                 // (measured: 65 536 images 264.2 us with, 262.1 without; mnist 189.9 / 180.2: off)
+#endif
 #ifndef SIB_SPLIT_ACC
 #define SIB_SPLIT_ACC 0
 #endif
@@ -433,6 +437,17 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             n_gs = SIB_DYN_SPANS ? __shfl_sync(0xffffffffu, n_raw, 0) : gs + kConv1Warps;
             span_src(n_gs, n_img0, n_lim, n_valid);
             n_src = n_valid ? chunk_ptr(n_img0, n_gs % N::SPANS, n_lim) : src;
+#if SIB_L2_BULK_PREFETCH
+            // One span (~7 us) ahead of its row loads, the one or two images the next span reads are pulled into L2 by a
+            // single bulk prefetch: the row loads then wait an L2 hit, not DRAM (the fp32 -> half conversion of a row
+            // was 4.5% of the conv1 warps' stall samples, waiting for its load).
+            if (n_valid && lane == 0) {
+                const int s2 = n_gs % N::SPANS;
+                const int first = min(n_img0 + (32 * s2) / N::OW1, n_lim - 1), last = min(n_img0 + (32 * s2 + 31) / N::OW1, n_lim - 1);
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(P.in + (size_t)first * N::IMG),
+                             "r"((uint32_t)((last - first + 1) * N::IMG * 4)) : "memory");
+            }
+#endif
         };
         constexpr int kResolveAt = N::REG_STAGE ? 3 : -1;  // the cp.async ring asks for n_valid from its first row on
         if (kResolveAt < 0) resolve_next();
