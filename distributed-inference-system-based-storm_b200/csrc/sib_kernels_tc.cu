@@ -341,6 +341,14 @@ __device__ __forceinline__ bool pair_images(const TcParams& P, int Qi, int& base
 #endif
 }
 
+// max that hands a NaN on (fmaxf drops it): an overflowed half-precision activation turns into Inf - Inf = NaN one layer
+// later, and that NaN has to reach the logits so that the margin guard sends the image to the fp32 path
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+    float d;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
+    return d;
+}
+
 #if SIB_CONV1_UMMA || SIB_CONV2_UMMA
 #include "sib_tc_umma.cuh"
 #endif
@@ -702,17 +710,17 @@ __device__ __forceinline__ void conv2_role(const TcParams& P, unsigned char* sme
             }
 #endif
             // pool over the column pair (rows g / g+8 of the tile)
-            const float h[4] = {fmaxf(c0[0] + d0[0], c0[2] + d0[2]), fmaxf(c0[1] + d0[1], c0[3] + d0[3]),
-                                fmaxf(c1[0] + d1[0], c1[2] + d1[2]), fmaxf(c1[1] + d1[1], c1[3] + d1[3])};
+            const float h[4] = {fmax_nan(c0[0] + d0[0], c0[2] + d0[2]), fmax_nan(c0[1] + d0[1], c0[3] + d0[3]),
+                                fmax_nan(c1[0] + d1[0], c1[2] + d1[2]), fmax_nan(c1[1] + d1[1], c1[3] + d1[3])};
             if ((oh & 1) == 0) {
 #pragma unroll
                 for (int i = 0; i < 4; i++) prev[i] = h[i];
             } else {
                 const int ph = oh >> 1;
-                const float v0 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[0], prev[0]), 0.f) : fmaxf(fmaxf(h[0], prev[0]) + bias00, 0.f);
-                const float v1 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[1], prev[1]), 0.f) : fmaxf(fmaxf(h[1], prev[1]) + bias01, 0.f);
-                const float v2 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[2], prev[2]), 0.f) : fmaxf(fmaxf(h[2], prev[2]) + bias10, 0.f);
-                const float v3 = SIB_BIAS_IN_ACC2 ? fmaxf(fmaxf(h[3], prev[3]), 0.f) : fmaxf(fmaxf(h[3], prev[3]) + bias11, 0.f);
+                const float v0 = SIB_BIAS_IN_ACC2 ? fmax_nan(fmax_nan(h[0], prev[0]), 0.f) : fmax_nan(fmax_nan(h[0], prev[0]) + bias00, 0.f);
+                const float v1 = SIB_BIAS_IN_ACC2 ? fmax_nan(fmax_nan(h[1], prev[1]), 0.f) : fmax_nan(fmax_nan(h[1], prev[1]) + bias01, 0.f);
+                const float v2 = SIB_BIAS_IN_ACC2 ? fmax_nan(fmax_nan(h[2], prev[2]), 0.f) : fmax_nan(fmax_nan(h[2], prev[2]) + bias10, 0.f);
+                const float v3 = SIB_BIAS_IN_ACC2 ? fmax_nan(fmax_nan(h[3], prev[3]), 0.f) : fmax_nan(fmax_nan(h[3], prev[3]) + bias11, 0.f);
                 uint16_t* dst = p2 + o2 + ph * N::PW2 * N::C2;
                 *reinterpret_cast<uint32_t*>(dst) = Ops<T>::pack(v0, v1);      // channels 2t, 2t+1
                 *reinterpret_cast<uint32_t*>(dst + 8) = Ops<T>::pack(v2, v3);  // channels 8+2t, 9+2t
@@ -784,8 +792,8 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
             for (int j = 0; j < N::NT1; j++) {
                 const int n0 = j * 8 + 2 * t;
                 const float b0 = bias[24 + n0], b1 = bias[24 + n0 + 1];
-                const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
-                const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
+                const float v0 = fmax_nan(acc[j][0] + b0, 0.f), v1 = fmax_nan(acc[j][1] + b1, 0.f);
+                const float v2 = fmax_nan(acc[j][2] + b0, 0.f), v3 = fmax_nan(acc[j][3] + b1, 0.f);
                 *reinterpret_cast<uint32_t*>(h1 + g * N::H1_STRIDE + n0) = Ops<T>::pack(v0, v1);
                 *reinterpret_cast<uint32_t*>(h1 + (g + 8) * N::H1_STRIDE + n0) = Ops<T>::pack(v2, v3);
                 if (dump) {
@@ -817,8 +825,8 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
             for (int j = 0; j < 12; j++) {
                 const int n0 = j * 8 + 2 * t;
                 const float b0 = bias[152 + n0], b1 = bias[152 + n0 + 1];
-                const float v0 = fmaxf(acc[j][0] + b0, 0.f), v1 = fmaxf(acc[j][1] + b1, 0.f);
-                const float v2 = fmaxf(acc[j][2] + b0, 0.f), v3 = fmaxf(acc[j][3] + b1, 0.f);
+                const float v0 = fmax_nan(acc[j][0] + b0, 0.f), v1 = fmax_nan(acc[j][1] + b1, 0.f);
+                const float v2 = fmax_nan(acc[j][2] + b0, 0.f), v3 = fmax_nan(acc[j][3] + b1, 0.f);
                 *reinterpret_cast<uint32_t*>(h2 + g * N::H2_STRIDE + n0) = Ops<T>::pack(v0, v1);
                 *reinterpret_cast<uint32_t*>(h2 + (g + 8) * N::H2_STRIDE + n0) = Ops<T>::pack(v2, v3);
             }
@@ -888,7 +896,7 @@ __device__ __forceinline__ void fc_pair(const TcParams& P, unsigned char* smem, 
                         if (P.argmax) P.argmax[img] = am;
                         const float mg = mx - second;
                         if (P.margin) P.margin[img] = mg;
-                        if (P.list && (!(mg >= P.tau * fmaxf(1.f, fabsf(mx) * (1.f / 12.f))) || !(fabsf(mx) <= 3.0e38f))) {  // guard: recompute in fp32 (threshold grows with the logits; a NaN margin is listed too)
+                        if (P.list && (!(mg >= P.tau * fmaxf(1.f, fabsf(mx) * (1.f / 12.f))) || !(fabsf(mx) <= 3.0e38f) || !(s <= 3.0e38f))) {  // guard: recompute in fp32 (threshold grows with the logits; a NaN margin is listed too, and so is a NaN anywhere among the logits: it makes the softmax sum NaN)
                             const int pos = atomicAdd(P.count, 1);
                             if (pos < P.n) P.list[pos] = img;
                         }

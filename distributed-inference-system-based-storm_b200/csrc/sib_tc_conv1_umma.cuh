@@ -127,7 +127,7 @@ __device__ __forceinline__ void conv1u_worker(const TcParams& P, unsigned char* 
         mbar_arrive(&d_empty[dp]);
         float v[N::C1];
 #pragma unroll
-        for (int c = 0; c < N::C1; c++) v[c] = fmaxf(fmaxf(fmaxf(e0[c], o0[c]), fmaxf(e1[c], o1[c])) + bias[c], 0.f);
+        for (int c = 0; c < N::C1; c++) v[c] = fmax_nan(fmax_nan(fmax_nan(e0[c], o0[c]), fmax_nan(e1[c], o1[c])) + bias[c], 0.f);
         uint16_t* dst = p1 + o_p1 + j * N::P1_ROW;  // shadow lanes hold the last live lane's values: same store
 #pragma unroll
         for (int c = 0; c < N::C1; c += 2) *reinterpret_cast<uint32_t*>(dst + c) = Ops<T>::pack(v[c], v[c + 1]);

@@ -76,14 +76,6 @@ template <typename T> __device__ __forceinline__ constexpr uint32_t umma_idesc_m
     return (1u << 4) | (fmt << 7) | (fmt << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
 }
 
-// max that hands a NaN on (fmaxf drops it): an overflowed half-precision activation turns into Inf - Inf = NaN one layer
-// later, and that NaN has to reach the logits so that the margin guard sends the image to the fp32 path
-__device__ __forceinline__ float fmax_nan(float a, float b) {
-    float d;
-    asm("max.NaN.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b));
-    return d;
-}
-
 // barriers by shared-memory address
 __device__ __forceinline__ void mbar_arrive_s(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
