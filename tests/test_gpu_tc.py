@@ -263,6 +263,33 @@ def test_overflowing_activations_fall_to_the_fp32_guard(sib, oracle, presets):
     assert st.guard_recomputed >= int(clear.sum()) // 2   # (nearly) everything went through the guard
 
 
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+def test_pixels_beyond_the_half_range_fall_to_the_fp32_guard(sib, oracle, presets, name):
+    """A pixel of +-1e5 is a legal JSON number and finite for the reference's fp32 graph, but Inf as a half. Its image
+    must come back as the fp32 network's answer: the Inf reaches the logits as Inf/NaN through the convolutions (the
+    epilogues hand NaN on) and a non-finite logit lists the image for the fp32 recompute."""
+    m = presets[name]
+    n = 96
+    x = sib.modelspec.synthetic_images(m, 74, n).copy()
+    rng = np.random.default_rng(5)
+    hit = np.arange(0, n, 3)
+    for i in hit:   # one to three out-of-range pixels per hit image, anywhere, either sign
+        for _ in range(int(rng.integers(1, 4))):
+            x[i, rng.integers(0, m.h), rng.integers(0, m.w), rng.integers(0, m.c)] = float(rng.choice([1.0e5, -1.0e5, 7.0e4]))
+    lg, pr = oracle.Model(m.to_blob()).forward(x, threads=0)
+    assert np.isfinite(lg).all()
+    with sib.native.Engine(m.to_blob(), precision=sib.native.PREC_FP16, max_batch=n, guard=True) as e:
+        gp, gl, ga = e.forward_sync(x)
+        st = e.stats()
+    assert st.guard_recomputed >= len(hit)
+    scale = np.maximum(1.0, np.abs(lg).max(1, keepdims=True))
+    assert (np.abs(gl[hit] - lg[hit]) / scale[hit]).max() <= 1e-5      # the hit images: fp32 logits
+    assert np.abs(gl - lg).max() <= 3e-2 * scale.max() and np.isfinite(gl).all()
+    s = np.sort(lg.astype(np.float64), 1)
+    clear = s[:, -1] - s[:, -2] > 1e-4 * scale[:, 0]
+    assert (ga[clear] == lg.argmax(1)[clear]).all()
+
+
 def test_half_range_check_on_weights(sib, presets):
     m = _scaled_model(sib, presets["mnist-lenet5"], 2, 1.0e7)
     with pytest.raises(sib.native.SibError):
