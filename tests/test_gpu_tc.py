@@ -263,7 +263,7 @@ def test_overflowing_activations_fall_to_the_fp32_guard(sib, oracle, presets):
     assert st.guard_recomputed >= int(clear.sum()) // 2   # (nearly) everything went through the guard
 
 
-@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5"])
+@pytest.mark.parametrize("name", ["mnist-lenet5", "cifar-lenet5", "mnist-wide", "cifar-wide"])
 def test_pixels_beyond_the_half_range_fall_to_the_fp32_guard(sib, oracle, presets, name):
     """A pixel of +-1e5 is a legal JSON number and finite for the reference's fp32 graph, but Inf as a half. Its image
     must come back as the fp32 network's answer: the Inf reaches the logits as Inf/NaN through the convolutions (the
