@@ -71,6 +71,11 @@ namespace {
 #define SIB_L2_BULK_PREFETCH 0   // conv1: one cp.async.bulk.prefetch.L2 per span for the images the warp's next span reads
                                  // (measured: 65 536 images 264.2 us with, 262.1 without; mnist 189.9 / 180.2: off)
 #endif
+#ifndef SIB_CONV1_NANMAX
+#define SIB_CONV1_NANMAX 1      // conv1's pool and ReLU hand a NaN on (FMNMX.NAN / FMNMX3.NAN, the same instruction count as fmaxf:
+                                // 260.2 us per 65 536 images against 262.0) like the later stages' do: a NaN pixel, or Inf - Inf of
+                                // two pixels beyond the half range, reaches the logits and the guard
+#endif
 #ifndef SIB_SPLIT_ACC
 #define SIB_SPLIT_ACC 0
 #endif
@@ -349,6 +354,12 @@ __device__ __forceinline__ float fmax_nan(float a, float b) {
     return d;
 }
 
+__device__ __forceinline__ float fmax_nan3(float a, float b, float c) {
+    float d;
+    asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 #if SIB_CONV1_UMMA || SIB_CONV2_UMMA
 #include "sib_tc_umma.cuh"
 #endif
@@ -457,7 +468,10 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
             }
 #endif
         };
-        constexpr int kResolveAt = N::REG_STAGE ? 3 : -1;  // the cp.async ring asks for n_valid from its first row on
+#ifndef SIB_RESOLVE_AT
+#define SIB_RESOLVE_AT 1   // measured: 1 -> 260.0 us per 65 536 images, 3 -> 262.0, 8 -> 269.2
+#endif
+        constexpr int kResolveAt = N::REG_STAGE ? SIB_RESOLVE_AT : -1;  // the cp.async ring asks for n_valid from its first row on
         if (kResolveAt < 0) resolve_next();
         // A span whose first column already lies past the last image has nothing to compute (the tail of a batch:
         // with 1 image in a launch, 13 of the pair's 14 spans). It only keeps the slot protocol going. Image indices
@@ -573,7 +587,7 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
                 float m[4];
 #pragma unroll
                 for (int i = 0; i < 4; i++)  // pool over the column pair (x + 0.f is not a no-op to the compiler: no dead adds)
-                    m[i] = SIB_SPLIT_ACC ? fmaxf(cE[i] + dE[i], cO[i] + dO[i]) : fmaxf(cE[i], cO[i]);
+                    m[i] = SIB_SPLIT_ACC ? fmaxf(cE[i] + dE[i], cO[i] + dO[i]) : SIB_CONV1_NANMAX ? ((oh & 1) ? fmax_nan3(cE[i], cO[i], prev[i]) : fmax_nan(cE[i], cO[i])) : fmaxf(cE[i], cO[i]);
                 if ((oh & 1) == 0) {
 #pragma unroll
                     for (int i = 0; i < 4; i++) prev[i] = m[i];
@@ -581,10 +595,10 @@ __device__ __forceinline__ void conv1_role(const TcParams& P, unsigned char* sme
                     const int ph = oh >> 1;
                     // relu(max(.)+b) == max over the window of relu(.+b)
                     const float pb0 = SIB_BIAS_IN_ACC1 ? 0.f : bias0, pb1 = SIB_BIAS_IN_ACC1 ? 0.f : bias1;
-                    const float v0 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[0], prev[0]), 0.f) : fmaxf(fmaxf(m[0], prev[0]) + pb0, 0.f);
-                    const float v1 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[1], prev[1]), 0.f) : fmaxf(fmaxf(m[1], prev[1]) + pb1, 0.f);
-                    const float v2 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[2], prev[2]), 0.f) : fmaxf(fmaxf(m[2], prev[2]) + pb0, 0.f);
-                    const float v3 = SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[3], prev[3]), 0.f) : fmaxf(fmaxf(m[3], prev[3]) + pb1, 0.f);
+                    const float v0 = SIB_CONV1_NANMAX ? fmax_nan(m[0] + pb0, 0.f) : SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[0], prev[0]), 0.f) : fmaxf(fmaxf(m[0], prev[0]) + pb0, 0.f);
+                    const float v1 = SIB_CONV1_NANMAX ? fmax_nan(m[1] + pb1, 0.f) : SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[1], prev[1]), 0.f) : fmaxf(fmaxf(m[1], prev[1]) + pb1, 0.f);
+                    const float v2 = SIB_CONV1_NANMAX ? fmax_nan(m[2] + pb0, 0.f) : SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[2], prev[2]), 0.f) : fmaxf(fmaxf(m[2], prev[2]) + pb0, 0.f);
+                    const float v3 = SIB_CONV1_NANMAX ? fmax_nan(m[3] + pb1, 0.f) : SIB_BIAS_IN_ACC1 ? fmaxf(fmaxf(m[3], prev[3]), 0.f) : fmaxf(fmaxf(m[3], prev[3]) + pb1, 0.f);
                     if (t < 3) {
                         *reinterpret_cast<uint32_t*>(p1 + o0 + ph * N::P1_ROW) = Ops<T>::pack(v0, v1);
                         *reinterpret_cast<uint32_t*>(p1 + o1 + ph * N::P1_ROW) = Ops<T>::pack(v2, v3);
