@@ -21,6 +21,8 @@
 //                    N; epilogues on the workers and the head warp; softmax / argmax / top1-top2 margin and the margin
 //                    guard's compaction list on the head warp.
 //   * the dense-layer operands (119 KB) arrive by cp.async.bulk on an mbarrier; only the dense head waits for them;
+//   * whole 16-image pairs are dealt to the CTAs round-robin, what is left after the last full round in equal runs of
+//     images to all of them (pair_images): a small launch uses one SM per image, a large one ends on all SMs at once;
 //   * conv1 stays on mma.sync: its N = 6, K = 75 contraction has no cheap operand path to tcgen05 -- from shared memory an
 //     M128 x K16 operand costs 39-48 clk per mma, through registers (tcgen05.st: SIB_CONV1_UMMA, 208 M img/s) the im2col
 //     rows cost more instructions than the mma save, and tcgen05.cp builds them exactly but at 64 clk per copy, unoverlapped

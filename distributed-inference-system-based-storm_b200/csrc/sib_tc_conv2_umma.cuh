@@ -9,18 +9,25 @@
 // so the im2col expansion (kw only) exists once per input row, in TMEM, and never in shared memory.
 //
 // Shape. One 8-image p1 slot = one M tile. TMEM lane = (image, output column): a worker warp owns the lanes of its
-// lane quadrant = the columns of 3 (cifar) or 4 (mnist) images; 30 or 32 live lanes.
-//   worker warps (q = 0..NWORK-1), per p1 row r:
-//        16 x LDS.32 (halves [6 ow, 6 ow + 32) of the row: 30 real K + 2 that meet zero weights) -> tcgen05.st x16
-//        -> a_full[r]; two rows behind the mma, per output-row pair: tcgen05.ld both rows -> max -> lane-pair
-//        exchange (the pool's other column) -> +bias, ReLU -> one 16-byte store of 8 channels into p2
-//   issuer warp: per p1 row up to 10 mma (5 kernel rows x 2 K steps) + tcgen05.commit -> a_free[r], d_full[pair]
+// lane quadrant = the columns of 3 (cifar) or 4 (mnist) images; 30 or 32 live lanes. Work goes by PAIRS of p1 rows.
+//   worker warps (two sets of q = 0..NWORK-1; set s takes the row pairs rp with rp % 2 == s), per tile:
+//        first every row pair of the set: 2 x 15 LDS.32 (halves [6 ow, 6 ow + 30) of both rows; K slots 30, 31 are 1.0
+//        and meet the bias in kernel row 0's B tile) -> one tcgen05.st x32 -> a_full[rp]; the p1 slot goes back to conv1
+//        after the set's last row pair (both sets arrive on p1_empty);
+//        then every output-row pair of the set: tcgen05.ld x32 of both rows -> max (NaN-propagating) -> lane-pair
+//        exchange (the pool's other column) -> ReLU -> one 16-byte store of 8 channels into p2, which is the dense head's
+//        B operand (144 bytes between K chunks: the lanes of that store differ in the K chunk); between the two phases
+//        and after them the set's share of the dense head's epilogues (sib_tc_fc_umma.cuh)
+//   issuer warp: per p1 row pair 12 mma (the even row through the stacked filter blocks 4|2|0 with N = 32, so one mma adds
+//        it into BOTH rows of an output pair; the odd row through 3|1 and, alone, 0) + tcgen05.commit -> a_free[rp],
+//        d_full[output pair rp - 2]
 // A lone warp retires about one instruction per 3.5 clk on this dependent code, so the roles are split so that no warp
 // carries more than ~1000 instructions per tile (first version: the third worker also issued; it ran 1500 clk per row
-// and the whole kernel at half speed, profiles/ncu_tc_r02_notes.md), the row loops are unrolled (A slot = row, constant
-// addresses) and barriers are addressed by their shared-memory offset (no generic-to-shared conversion per wait).
+// and the whole kernel at half speed, profiles/ncu_tc_r02_notes.md), barriers are addressed by their shared-memory
+// offset (no generic-to-shared conversion per wait), and the row-pair loops are ROLLED: unrolled, the kernel's roles
+// together overflowed the instruction cache (72% hit rate).
 // TMEM: 14 A rows x 16 columns (slot = row; a tile's rows go in while the previous tile's last mma still run) +
-// a ring of 8 output-row pairs x 2 x 16 columns = 480 of 512 columns.
+// a ring of 8 output-row pairs x 2 x 16 columns = 480 of 512 columns; the dense head's accumulator takes the last 16.
 #pragma once
 
 template <typename N>
