@@ -825,7 +825,9 @@ extern "C" int sib_poll_json_batch(sib_engine* e, char* arena, size_t cap, uint6
         if (res[i].status == SIB_OK && res[i].probs) {
             const long len = json_encode(res[i].probs, res[i].n, res[i].n_classes, arena + at, cap - at);
             if (len > 0) at += (size_t)len;          // written without a terminating NUL: the offsets delimit it
-            else status[i] = (int32_t)(len < 0 ? len : SIB_ECAP);  // cannot happen: the bound was reserved above
+            else status[i] = (int32_t)(len < 0 ? len : SIB_ECAP);  // only the first tuple of a poll can get here, when its message alone
+                                                                   // (hundreds of images in one tuple) is larger than the arena: it is
+                                                                   // reported, not queued for ever
         }
     }
     if (n >= 0) offsets[n] = (uint32_t)at;
