@@ -543,7 +543,12 @@ int sibo_float_to_string(float x, char *buf) {
             snprintf(u, sizeof u, "%llde%d", mm, ee - (p - 1));
             if (strtof(u, NULL) != x) continue;
             double err = fabs(strtod(u, NULL) - (double)x);
-            if (err < best_err || (err == best_err && (mm % 2 == 0))) { best_err = err; best_m = mm; best_e = ee; }
+            /* Two candidates exactly as close (x = 2^-12 = 2.44140625E-4 lies midway between ..062 and ..063): the even
+             * last digit wins (Float.toString's specification since JDK 19; Ryu and std::to_chars agree). The two
+             * errors are computed in double, where neither decimal is exact, so "as close" is "equal to 1e-6 of the
+             * error": a real difference between two candidates one unit apart is never that small for a 24-bit x. */
+            int tie = best_m > 0 && fabs(err - best_err) <= 1e-6 * best_err;
+            if ((!tie && err < best_err) || (tie && (mm % 2 == 0))) { best_err = err; best_m = mm; best_e = ee; }
         }
         if (best_m > 0) {
             char u[32];

@@ -56,6 +56,11 @@ TOSTRING_KAT = [
     (2.0e-3, "0.002"), (9.999999e-4, "9.999999E-4"), (1.0e-3, "0.001"), (16777216.0, "1.6777216E7"),
     (0.33333334, "0.33333334"), (1.0e-10, "1.0E-10"), (float("nan"), '"NaN"'), (float("inf"), '"Infinity"'),
     (float("-inf"), '"-Infinity"'),
+    # exact ties: the float lies midway between the two shortest decimals; Float.toString (JDK >= 19 specification),
+    # Ryu and std::to_chars take the even last digit. The oracle once broke these ties by double rounding noise
+    # (found by tests/fuzz_codec_diff.cpp: 2^-12 printed as 2.4414063E-4).
+    (2.0 ** -12, "2.4414062E-4"), (0.00146484375, "0.0014648438"), (0.00732421875, "0.0073242188"),
+    (0.244140625, "0.24414062"), (2.44140625, "2.4414062"), (24.4140625, "24.414062"), (0.00439453125, "0.0043945312"),
 ]
 
 
