@@ -197,7 +197,7 @@ bool const_tensor(const Node& nd, Tensor* out, std::string* why) {
         else if (f == 2 && t == 2) { if (!shape_dims(b, &out->dims)) { *why = "'" + nd.name + "': unknown rank"; return false; } }
         else if (f == 4 && t == 2) content = b;
         else if (f == 5 && t == 5) { float x; uint32_t u = (uint32_t)v; std::memcpy(&x, &u, 4); vals.push_back(x); }
-        else if (f == 5 && t == 2) { vals.resize(b.n / 4); if (b.n) std::memcpy(vals.data(), b.p, b.n / 4 * 4); }
+        else if (f == 5 && t == 2) { vals.resize(b.n / 4); if (b.n >= 4) std::memcpy(vals.data(), b.p, b.n / 4 * 4); }  // (1..3 stray bytes: no element, no copy from a null vector)
     }
     if (r.bad || dtype != 1) { *why = "Const '" + nd.name + "' is not a DT_FLOAT tensor"; return false; }
     size_t numel = 1;

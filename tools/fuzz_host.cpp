@@ -108,6 +108,7 @@ std::vector<uint8_t> read_file(const char* path) {
 
 int main(int argc, char** argv) {
     const double seconds = argc > 1 ? std::atof(argv[1]) : 10.0;
+    if (const char* sd = std::getenv("FUZZ_SEED")) g_s = std::strtoull(sd, nullptr, 0);  // another stream of mutations
     std::vector<std::vector<uint8_t>> pb_seeds, blob_seeds;
     for (int i = 2; i < argc; i++) {
         auto b = read_file(argv[i]);
